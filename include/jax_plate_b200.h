@@ -1,0 +1,141 @@
+/* C-ABI of libjaxplate_b200.so -- the drop-in boundary for jax_plate's frequency-domain
+ * forward / adjoint / gradient hot path on B200 (sm_100a).
+ *
+ * What each entry point replaces in the reference (paths relative to /root/reference):
+ *
+ *   jpb_add_mat        InnerState::add_mat<T,I>           source/jax_plate_lib/include/InnerState.h:120-162
+ *                      (+ umfpack::symbolic               source/jax_plate_lib/include/umfpack_interface.h:42-52)
+ *   jpb_solve          InnerState::solve<T,I>             InnerState.h:164-308   (mode table :187-232)
+ *   jpb_matvec         InnerState::matvec<T,I>            InnerState.h:310-470, csc_matvec.h:31-66
+ *   jpb_assemble       XLA-CPU assembly in Problem._solve source/jax_plate/Problem.py:440-445
+ *   jpb_register_components / jpb_eval_forward / jpb_eval_loss_grad
+ *                      the whole per-frequency body of Problem._solve + its reverse-mode
+ *                      derivative: Problem.py:437-477 (assembly, rhs, solve, read-out),
+ *                      Problem.py:948-975 (losses), Sparse.py:162-176,200-222 (AD rules)
+ *
+ * Conventions
+ *   - complex128 arrays are passed as packed (re, im) pairs of doubles, like the reference
+ *     passes them to UMFPACK (umfpack_interface.h:50-51: Az = NULL).
+ *   - all array arguments are HOST pointers unless the function name ends in `_dev`;
+ *     they are borrowed for the duration of the call; results are written into
+ *     caller-allocated buffers.
+ *   - every function returns 0 on success and a non-zero JPB_E* code otherwise;
+ *     jpb_last_error() returns the message (the reference throws std::runtime_error,
+ *     umfpack_interface.h:11-18; the Python layer turns codes into RuntimeError).
+ *   - a state is bound to one CUDA device; calls on one state must not overlap.
+ *   - there is no CPU fallback: without a usable CUDA device jpb_create fails.
+ */
+#ifndef JAX_PLATE_B200_H
+#define JAX_PLATE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct jpb_state jpb_state;
+
+enum {
+    JPB_OK = 0,
+    JPB_EINVAL = 1,    /* bad argument / shape / mode (reference: runtime_error "Invalid `mode`") */
+    JPB_ECUDA = 2,     /* CUDA runtime failure */
+    JPB_ESINGULAR = 3, /* a system was numerically singular (reference: UMFPACK status != 0) */
+    JPB_ENOMEM = 4,
+    JPB_ESTATE = 5     /* call sequence error (e.g. components not registered) */
+};
+
+/* loss types of Problem.getLossFunction (Problem.py:948-975) */
+enum { JPB_LOSS_MSE = 0, JPB_LOSS_RMSE = 1, JPB_LOSS_MSE_AFC = 2, JPB_LOSS_MSE_LOG_AFC = 3 };
+
+/* ---- life cycle ------------------------------------------------------------------- */
+int jpb_create(jpb_state** out, int device);
+void jpb_destroy(jpb_state* st);
+const char* jpb_last_error(const jpb_state* st);
+/* upper bound of device memory (bytes) the state may use for fronts/workspaces;
+ * 0 = 80 % of what is free at first use */
+int jpb_set_memory_budget(jpb_state* st, int64_t bytes);
+/* iterative-refinement steps applied after every triangular solve (default 1) */
+int jpb_set_refinement(jpb_state* st, int steps);
+
+/* ---- pattern registration (InnerState::add_mat) ------------------------------------
+ * indices/indptr: CSC of the N x N pattern; indices_T/indptr_T/perm: the reference's CSR
+ * view and CSR->CSC permutation (Sparse.py:33-34).  Only the CSC arrays are used for the
+ * analysis; the CSR view is rebuilt exactly (so transposed products are right for
+ * structurally unsymmetric patterns too) and `perm`, when given, is checked against it.
+ * index_bytes = 4 or 8.  *solver_num receives the 0-based handle (insertion index). */
+int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, const void* indptr,
+                const void* indices_T, const void* indptr_T, const void* perm, int index_bytes,
+                int* solver_num);
+
+/* symbolic statistics: info[0]=N, [1]=nnz, [2]=nnz(L+U), [3]=real flops of one numeric
+ * factorisation, [4]=front slots (complex elements per system), [5]=#fronts, [6]=#levels,
+ * [7]=largest front order, [8]=largest pivot block, [9]=vector workspace slots */
+int jpb_symbolic_info(const jpb_state* st, int solver_num, double* info10);
+/* fill-reducing permutation found by the analysis: perm[new] = old, length N */
+int jpb_get_ordering(const jpb_state* st, int solver_num, int32_t* perm);
+
+/* ---- InnerState::solve / matvec ----------------------------------------------------
+ * mode table (Sparse.py:238-277, InnerState.h:187-232):
+ *   0: data[nnz]      b[N]         -> out[N]
+ *   1: data[B,nnz]    b[N]         -> out[B,N]
+ *   2: data[nnz]      b[B,N]       -> out[B,N]      (one factorisation, B right-hand sides)
+ *   3: data[B,nnz]    b[B,N]       -> out[B,N]
+ *   4: data[B1,nnz]   b[B0,B1,N]   -> out[B0,B1,N]  (B1 factorisations, B0 rhs each)
+ * nbatch0 = B (modes 1-3) or B0 (mode 4); nbatch1 = B1 (mode 4 only).
+ * transpose != 0 solves A^T x = b (plain transpose, UMFPACK_Aat, InnerState.h:183-185).
+ * status (optional, one int per system): 0 ok, 1 singular pivot block encountered. */
+int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const double* data,
+              const double* b, int64_t nbatch0, int64_t nbatch1, double* out, int* status);
+int jpb_matvec(jpb_state* st, int solver_num, int mode, int transpose, const double* mat,
+               const double* vec, int64_t nbatch0, int64_t nbatch1, double* out);
+
+/* data[b,e] = sum_k coef[b,k] * mats[k,e]   (Problem.py:440-445), coef complex, mats real */
+int jpb_assemble(jpb_state* st, int64_t nnz, int K, int64_t B, const double* mats,
+                 const double* coef, double* data);
+
+/* ---- fused per-frequency evaluation -------------------------------------------------
+ * mats [K,nnz] real in the canonical CSC order, rhs_vec [N] real, Q [R,N] real read-out
+ * rows (row means of the interpolation matrices, Problem.py:454-462).  Kept on the device. */
+int jpb_register_components(jpb_state* st, int solver_num, int K, const double* mats,
+                            const double* rhs_vec, int R, const double* Q);
+
+/* For b < B: A_b = sum_k coef[b,k] M_k ; u_b = A_b^-1 (rhs_scale[b] * rhs_vec) ;
+ * y[b,r] = Q_r . u_b.  u (optional) [B,N] complex, y [B,R] complex. */
+int jpb_eval_forward(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                     const double* rhs_scale, double* u, double* y, int* status);
+
+/* Forward + adjoint + gradient for the unsymm read-out  fr = sqrt(sum_r w[r] |y_r|^2)
+ * (Problem.py:464-477) and loss `loss_type` against ref[B] with mean over F_total
+ * frequencies (F_total >= B allows sharding one sweep over several calls / GPUs):
+ *   fr[B] real; loss_sum = sum_b loss term (caller divides by F_total);
+ *   ct_coef[B,K] complex = -lambda_b^T M_k u_b ; ct_s[B] complex = lambda_b^T rhs_vec
+ * with lambda_b = A_b^-T ubar_b, ubar_b the JAX-convention cotangent of u_b
+ * (SURVEY App. D).  One numeric factorisation per system serves both solves. */
+int jpb_eval_loss_grad(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                       const double* rhs_scale, const double* ref, const double* w,
+                       int loss_type, int64_t F_total, double* fr, double* loss_sum,
+                       double* ct_coef, double* ct_s, int* status);
+
+/* same as jpb_eval_loss_grad with every array already in device memory (zero-copy for
+ * torch tensors); runs on `stream` (a cudaStream_t) without synchronising the host. */
+int jpb_eval_loss_grad_dev(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                           const double* rhs_scale, const double* ref, const double* w,
+                           int loss_type, int64_t F_total, double* fr, double* loss_sum,
+                           double* ct_coef, double* ct_s, int* status, void* stream);
+
+/* ---- instrumentation ----------------------------------------------------------------
+ * phase timers (ms, CUDA events on the state's stream) of the last jpb_eval_* / jpb_solve
+ * call: [0] factor, [1] forward solve(s), [2] adjoint solve(s), [3] residual/refinement
+ * SpMV, [4] gradient, [5] read-out/loss, [6] H2D, [7] D2H; [8] kernel launches issued;
+ * [9] systems per wave */
+int jpb_last_timings(const jpb_state* st, double* t10);
+/* FP64 tensor-core (DMMA m8n8k4) peak of this device in TFLOP/s, register-resident loop */
+int jpb_dmma_peak(jpb_state* st, double* tflops);
+/* self test of the dense-front kernels against scalar device loops; returns max rel err */
+int jpb_selftest(jpb_state* st, double* max_err);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,119 @@
+"""ctypes binding of libjaxplate_b200.so (the C-ABI in include/jax_plate_b200.h).
+
+There is no CPU fallback: if the shared library is missing, or no CUDA device can be
+opened, everything that computes raises.  Build the library with
+`python -c "import __graft_entry__ as g; g.build()"` (nvcc, sm_100a, in-tree).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libjaxplate_b200.so")
+
+JPB_OK, JPB_EINVAL, JPB_ECUDA, JPB_ESINGULAR, JPB_ENOMEM, JPB_ESTATE = range(6)
+LOSS_TYPES = {"MSE": 0, "RMSE": 1, "MSE_AFC": 2, "MSE_LOG_AFC": 3}
+
+# every symbol include/jax_plate_b200.h declares
+EXPORTED_SYMBOLS = (
+    "jpb_create", "jpb_destroy", "jpb_last_error", "jpb_set_memory_budget", "jpb_set_refinement",
+    "jpb_add_mat", "jpb_symbolic_info", "jpb_get_ordering", "jpb_solve", "jpb_matvec",
+    "jpb_assemble", "jpb_register_components", "jpb_eval_forward", "jpb_eval_loss_grad",
+    "jpb_eval_loss_grad_dev", "jpb_last_timings", "jpb_dmma_peak", "jpb_selftest",
+)
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """dlopen the in-tree CUDA library; raise (never fall back) when it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: the CUDA library has not been built "
+            "(run __graft_entry__.build()); plate_inverse_problem_b200 has no CPU fallback")
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, i64, dp = C.c_void_p, C.c_int, C.c_int64, C.c_void_p
+    lib.jpb_create.argtypes = [C.POINTER(vp), i32]
+    lib.jpb_destroy.argtypes = [vp]
+    lib.jpb_destroy.restype = None
+    lib.jpb_last_error.argtypes = [vp]
+    lib.jpb_last_error.restype = C.c_char_p
+    lib.jpb_set_memory_budget.argtypes = [vp, i64]
+    lib.jpb_set_refinement.argtypes = [vp, i32]
+    lib.jpb_add_mat.argtypes = [vp, i64, i64, dp, dp, dp, dp, dp, i32, C.POINTER(i32)]
+    lib.jpb_symbolic_info.argtypes = [vp, i32, dp]
+    lib.jpb_get_ordering.argtypes = [vp, i32, dp]
+    lib.jpb_solve.argtypes = [vp, i32, i32, i32, dp, dp, i64, i64, dp, dp]
+    lib.jpb_matvec.argtypes = [vp, i32, i32, i32, dp, dp, i64, i64, dp]
+    lib.jpb_assemble.argtypes = [vp, i64, i32, i64, dp, dp, dp]
+    lib.jpb_register_components.argtypes = [vp, i32, i32, dp, dp, i32, dp]
+    lib.jpb_eval_forward.argtypes = [vp, i32, i64, dp, dp, dp, dp, dp]
+    lib.jpb_eval_loss_grad.argtypes = [vp, i32, i64, dp, dp, dp, dp, i32, i64, dp, dp, dp, dp, dp]
+    lib.jpb_eval_loss_grad_dev.argtypes = [vp, i32, i64, dp, dp, dp, dp, i32, i64, dp, dp, dp, dp, dp, vp]
+    lib.jpb_last_timings.argtypes = [vp, dp]
+    lib.jpb_dmma_peak.argtypes = [vp, dp]
+    lib.jpb_selftest.argtypes = [vp, dp]
+    for name in EXPORTED_SYMBOLS:
+        if name not in ("jpb_destroy", "jpb_last_error"):
+            getattr(lib, name).restype = i32
+    _lib = lib
+    return lib
+
+
+def ptr(a):
+    """Raw data pointer of a C-contiguous numpy array (or None)."""
+    if a is None:
+        return None
+    assert a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class State:
+    """Owner of one `jpb_state` (one CUDA device)."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.jpb_create(C.byref(h), int(device))
+        if rc != JPB_OK:
+            raise RuntimeError(
+                f"jpb_create(device={device}) failed with code {rc}: no usable CUDA device "
+                "(plate_inverse_problem_b200 has no CPU fallback)")
+        self.h = h
+        self.device = int(device)
+
+    def check(self, rc: int):
+        if rc != JPB_OK:
+            msg = self.lib.jpb_last_error(self.h).decode()
+            raise RuntimeError(msg)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.jpb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def timings(self) -> dict:
+        t = np.zeros(10)
+        self.check(self.lib.jpb_last_timings(self.h, ptr(t)))
+        keys = ("factor_ms", "fwd_solve_ms", "adj_solve_ms", "spmv_ms", "grad_ms", "readout_ms",
+                "h2d_ms", "d2h_ms", "launches", "wave")
+        return dict(zip(keys, t.tolist()))
+
+    def symbolic_info(self, solver_num: int) -> dict:
+        t = np.zeros(10)
+        self.check(self.lib.jpb_symbolic_info(self.h, int(solver_num), ptr(t)))
+        keys = ("N", "nnz", "nnz_lu", "flops", "front_slots", "nfronts", "nlevels", "max_front",
+                "max_pivots", "vec_slots")
+        return dict(zip(keys, t.tolist()))

@@ -1,0 +1,948 @@
+// Host side of libjaxplate_b200.so: pattern registry, wave scheduling, kernel launches and
+// the C-ABI declared in include/jax_plate_b200.h.  Replaces jax_plate_lib's InnerState
+// (/root/reference/source/jax_plate_lib/include/InnerState.h:86-471) and the UMFPACK calls
+// behind it; see the header for the entry-point-by-entry-point mapping.
+#include "../../include/jax_plate_b200.h"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+#include "symbolic.h"
+
+using namespace jpb;
+
+namespace {
+
+struct CudaError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+#define CK(call)                                                                              \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess) {                                                              \
+            char buf_[512];                                                                   \
+            snprintf(buf_, sizeof buf_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                     __FILE__, __LINE__);                                                     \
+            throw CudaError(buf_);                                                            \
+        }                                                                                     \
+    } while (0)
+
+struct InvalidArg : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+struct StateError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+// grow-only device buffer
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    void* get(size_t bytes) {
+        if (bytes > cap) {
+            if (p) cudaFree(p);
+            p = nullptr;
+            cap = 0;
+            cudaError_t e = cudaMalloc(&p, bytes);
+            if (e != cudaSuccess) {
+                p = nullptr;
+                char buf[256];
+                snprintf(buf, sizeof buf, "cudaMalloc of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+                throw CudaError(buf);
+            }
+            cap = bytes;
+        }
+        return p;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    ~DevBuf() { release(); }
+};
+
+template <class T>
+T* upload(const std::vector<T>& v) {
+    T* d = nullptr;
+    size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
+    CK(cudaMalloc(&d, bytes));
+    if (!v.empty()) CK(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return d;
+}
+
+struct Pattern {
+    Symbolic S;
+    std::vector<int> levelptr;
+    // symbolic data on the device
+    FrontDesc* d_fr = nullptr;
+    int *d_rowidx_orig = nullptr, *d_children = nullptr, *d_relmap = nullptr, *d_ent_src = nullptr,
+        *d_ent_slot = nullptr, *d_levelfronts = nullptr;
+    // sparse views: CSC (as given) and CSR (rebuilt); *_pos_ent map into front-entry order
+    int *d_csc_ptr = nullptr, *d_csc_row = nullptr, *d_csc_col = nullptr, *d_csc_pos_ent = nullptr;
+    int *d_csr_ptr = nullptr, *d_csr_col = nullptr, *d_csr_pos = nullptr, *d_csr_pos_ent = nullptr;
+    // registered components
+    int K = 0, R = 0;
+    double *d_mats = nullptr, *d_mats_f = nullptr, *d_rhs_vec = nullptr, *d_Q = nullptr;
+    SymDev sd{};
+    int max_s = 0;
+
+    ~Pattern() {
+        void* ptrs[] = {d_fr, d_rowidx_orig, d_children, d_relmap, d_ent_src, d_ent_slot,
+                        d_levelfronts, d_csc_ptr, d_csc_row, d_csc_col, d_csc_pos_ent, d_csr_ptr,
+                        d_csr_col, d_csr_pos, d_csr_pos_ent, d_mats, d_mats_f, d_rhs_vec, d_Q};
+        for (void* p : ptrs)
+            if (p) cudaFree(p);
+    }
+};
+
+enum Phase { PH_FACTOR = 0, PH_FWD, PH_ADJ, PH_SPMV, PH_GRAD, PH_READOUT, PH_H2D, PH_D2H, PH_COUNT };
+
+struct TimedSpan {
+    int phase;
+    cudaEvent_t a, b;
+};
+
+}  // namespace
+
+struct jpb_state {
+    int device = 0;
+    cudaStream_t stream = nullptr;     // the state's own stream
+    std::vector<std::unique_ptr<Pattern>> pats;
+    std::string err;
+    int64_t budget = 0;
+    int refine = 1;
+    // workspaces
+    DevBuf F, V, vals, data, vb, vx, vr, vd, vlam, partial, small, hstage, status;
+    // instrumentation
+    std::vector<TimedSpan> spans;
+    std::vector<cudaEvent_t> pool;
+    size_t pool_used = 0;
+    double launches = 0;
+    double wave = 0;
+    bool timing = true;
+
+    ~jpb_state() {
+        for (auto e : pool) cudaEventDestroy(e);
+        if (stream) cudaStreamDestroy(stream);
+    }
+    cudaEvent_t ev() {
+        if (pool_used == pool.size()) {
+            cudaEvent_t e;
+            CK(cudaEventCreate(&e));
+            pool.push_back(e);
+        }
+        return pool[pool_used++];
+    }
+    void reset_timing() {
+        spans.clear();
+        pool_used = 0;
+        launches = 0;
+    }
+};
+
+namespace {
+
+struct Span {
+    jpb_state* st;
+    cudaStream_t s;
+    TimedSpan t;
+    bool on;
+    Span(jpb_state* st_, cudaStream_t s_, int phase) : st(st_), s(s_), on(st_->timing) {
+        if (!on) return;
+        t.phase = phase;
+        t.a = st->ev();
+        t.b = st->ev();
+        cudaEventRecord(t.a, s);
+    }
+    ~Span() {
+        if (!on) return;
+        cudaEventRecord(t.b, s);
+        st->spans.push_back(t);
+    }
+};
+
+int fail(jpb_state* st, int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (st) st->err = buf;
+    return code;
+}
+
+#define JPB_TRY(st) try {
+#define JPB_CATCH(st)                                                    \
+    }                                                                    \
+    catch (const InvalidArg& e) { return fail(st, JPB_EINVAL, "%s", e.what()); } \
+    catch (const StateError& e) { return fail(st, JPB_ESTATE, "%s", e.what()); } \
+    catch (const CudaError& e) { return fail(st, JPB_ECUDA, "%s", e.what()); }   \
+    catch (const std::bad_alloc&) { return fail(st, JPB_ENOMEM, "out of host memory"); } \
+    catch (const std::exception& e) { return fail(st, JPB_EINVAL, "%s", e.what()); }
+
+Pattern& pattern(jpb_state* st, int solver_num) {
+    if (!st) throw InvalidArg("null state");
+    if (solver_num < 0 || solver_num >= (int)st->pats.size())
+        throw InvalidArg("solver_num out of range (no such pattern registered)");
+    return *st->pats[solver_num];
+}
+
+int64_t budget_bytes(jpb_state* st) {
+    if (st->budget > 0) return st->budget;
+    size_t fr = 0, tot = 0;
+    CK(cudaMemGetInfo(&fr, &tot));
+    // memory already held by our grow-only workspaces is reusable
+    size_t held = st->F.cap + st->V.cap + st->vals.cap + st->data.cap + st->vb.cap + st->vx.cap +
+                  st->vr.cap + st->vd.cap + st->vlam.cap + st->partial.cap;
+    return (int64_t)((fr + held) * 0.8);
+}
+
+// ---------------------------------------------------------------------------- launches
+void launch_check(jpb_state* st) {
+    st->launches += 1;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) throw CudaError(std::string("kernel launch failed: ") + cudaGetErrorString(e));
+}
+
+// numeric factorisation of `nsys` systems into F
+void factor(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* F, const cd* data, const cd* coef,
+            cd* vals, int* status) {
+    Span span(st, s, PH_FACTOR);
+    const bool fused = data == nullptr;
+    for (int l = 0; l < P.S.nlevels; ++l) {
+        int nf = P.levelptr[l + 1] - P.levelptr[l];
+        int64_t grid = (int64_t)nf * nsys;
+        if (grid > 0x7fffffff) throw InvalidArg("wave too large for one launch");
+        const int* lf = P.d_levelfronts + P.levelptr[l];
+        if (fused)
+            factor_level_kernel<true><<<(unsigned)grid, FACTOR_THREADS, 0, s>>>(
+                P.sd, lf, nsys, F, nullptr, coef, P.d_mats_f, P.K, vals, status);
+        else
+            factor_level_kernel<false><<<(unsigned)grid, FACTOR_THREADS, 0, s>>>(
+                P.sd, lf, nsys, F, data, nullptr, nullptr, 0, nullptr, status);
+        launch_check(st);
+    }
+}
+
+// x(b, j) = A_b^-1 rhs(b, j)  (or A_b^-T)
+void tri_solve(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool trans, VecView vv, int phase) {
+    Span span(st, s, phase);
+    size_t smem = (size_t)P.max_s * sizeof(cd);
+    for (int l = 0; l < P.S.nlevels; ++l) {
+        int nf = P.levelptr[l + 1] - P.levelptr[l];
+        int64_t grid = (int64_t)nf * vv.nsys * vv.nrhs;
+        if (grid > 0x7fffffff) throw InvalidArg("wave too large for one launch");
+        const int* lf = P.d_levelfronts + P.levelptr[l];
+        if (trans)
+            fwd_level_kernel<true><<<(unsigned)grid, SOLVE_THREADS, smem, s>>>(P.sd, lf, F, vv);
+        else
+            fwd_level_kernel<false><<<(unsigned)grid, SOLVE_THREADS, smem, s>>>(P.sd, lf, F, vv);
+        launch_check(st);
+    }
+    for (int l = P.S.nlevels - 1; l >= 0; --l) {
+        int nf = P.levelptr[l + 1] - P.levelptr[l];
+        int64_t grid = (int64_t)nf * vv.nsys * vv.nrhs;
+        const int* lf = P.d_levelfronts + P.levelptr[l];
+        if (trans)
+            bwd_level_kernel<true><<<(unsigned)grid, SOLVE_THREADS, smem, s>>>(P.sd, lf, F, vv);
+        else
+            bwd_level_kernel<false><<<(unsigned)grid, SOLVE_THREADS, smem, s>>>(P.sd, lf, F, vv);
+        launch_check(st);
+    }
+}
+
+// y(b,j) = [rhs(b,j) -] op(A_b) x(b,j)
+void spmv(jpb_state* st, cudaStream_t s, Pattern& P, bool trans, const cd* vals, int64_t vals_sb,
+          bool vals_ent_order, const cd* x, int64_t x_sb, int64_t x_sj, const cd* rhs, int64_t rhs_sb,
+          int64_t rhs_sj, cd* y, int nsys, int nrhs) {
+    Span span(st, s, PH_SPMV);
+    const int* ptr = trans ? P.d_csc_ptr : P.d_csr_ptr;
+    const int* idx = trans ? P.d_csc_row : P.d_csr_col;
+    const int* pos = trans ? (vals_ent_order ? P.d_csc_pos_ent : nullptr)
+                           : (vals_ent_order ? P.d_csr_pos_ent : P.d_csr_pos);
+    dim3 grid((P.S.N + 127) / 128, (unsigned)(nsys * nrhs));
+    if ((int64_t)nsys * nrhs > 65535) throw InvalidArg("too many vectors for one spmv launch");
+    spmv_kernel<<<grid, 128, 0, s>>>(P.S.N, P.S.nnz, ptr, idx, pos, vals, vals_sb, x, x_sb, x_sj, rhs,
+                                     rhs_sb, rhs_sj, y, nsys);
+    launch_check(st);
+}
+
+// solve + iterative refinement.  x receives the solution in the dense (j*nsys + b) layout.
+void solve_refined(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool trans, const cd* vals,
+                   int64_t vals_sb, bool vals_ent_order, const cd* rhs, int64_t rhs_sb, int64_t rhs_sj,
+                   cd* x, cd* V, cd* r, cd* d, int nsys, int nrhs, int phase) {
+    VecView vv{rhs, rhs_sb, rhs_sj, x, V, nsys, nrhs};
+    tri_solve(st, s, P, F, trans, vv, phase);
+    for (int it = 0; it < st->refine; ++it) {
+        spmv(st, s, P, trans, vals, vals_sb, vals_ent_order, x, 1, nsys, rhs, rhs_sb, rhs_sj, r, nsys, nrhs);
+        VecView v2{r, 1, nsys, d, V, nsys, nrhs};
+        tri_solve(st, s, P, F, trans, v2, phase);
+        int64_t n = (int64_t)nsys * nrhs * P.S.N;
+        axpy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, x, d);
+        launch_check(st);
+    }
+}
+
+struct ModeShape {
+    int64_t nsys, nrhs;        // factorisations, right-hand sides per factorisation
+    int64_t rhs_sb, rhs_sj;    // strides (in vectors) of b for (system, rhs)
+};
+
+ModeShape decode_mode(int mode, int64_t nb0, int64_t nb1) {
+    switch (mode) {
+        case 0: return {1, 1, 0, 0};
+        case 1: if (nb0 < 1) break; return {nb0, 1, 0, 0};
+        case 2: if (nb0 < 1) break; return {1, nb0, 0, 1};
+        case 3: if (nb0 < 1) break; return {nb0, 1, 1, 0};
+        case 4: if (nb0 < 1 || nb1 < 1) break; return {nb1, nb0, 1, nb1};
+        default: throw InvalidArg("Invalid `mode` argument in InnerState::solve().");
+    }
+    throw InvalidArg("batch sizes must be positive");
+}
+
+void summarise_timings(const jpb_state* st, double* t) {
+    for (int i = 0; i < 10; ++i) t[i] = 0.0;
+    for (const TimedSpan& sp : st->spans) {
+        cudaEventSynchronize(sp.b);
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess) t[sp.phase] += ms;
+    }
+    t[8] = st->launches;
+    t[9] = st->wave;
+}
+
+// core of the fused evaluation; every pointer is a device pointer
+void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* coef, const cd* scale,
+               const double* ref, const double* w, int loss_type, int64_t F_total, cd* u_out, cd* y,
+               double* fr, double* loss_sum, cd* ct_coef, cd* ct_s, int* status, bool adjoint) {
+    if (P.K == 0) throw StateError("components not registered for this pattern (jpb_register_components)");
+    const int N = P.S.N;
+    const int64_t nnz = P.S.nnz;
+    const int K = P.K, R = P.R;
+    const int64_t nchunks = (nnz + GRAD_THREADS * GRAD_PER_THREAD - 1) / (GRAD_THREADS * GRAD_PER_THREAD);
+    // per-system workspace bytes
+    int64_t per = (P.S.front_slots + nnz + P.S.vec_slots + 5 * (int64_t)N) * 16 + nchunks * K * 16 + 256;
+    int64_t W = std::max<int64_t>(1, std::min<int64_t>(B, budget_bytes(st) / per));
+    W = std::min<int64_t>(W, 65535);
+    st->wave = (double)W;
+    cd* F = (cd*)st->F.get((size_t)W * P.S.front_slots * 16);
+    cd* vals = (cd*)st->vals.get((size_t)W * nnz * 16);
+    cd* V = (cd*)st->V.get((size_t)W * P.S.vec_slots * 16);
+    cd* vb = (cd*)st->vb.get((size_t)W * N * 16);
+    cd* vx = (cd*)st->vx.get((size_t)W * N * 16);
+    cd* vr = (cd*)st->vr.get((size_t)W * N * 16);
+    cd* vd = (cd*)st->vd.get((size_t)W * N * 16);
+    cd* vlam = (cd*)st->vlam.get((size_t)W * N * 16);
+    cd* partial = adjoint ? (cd*)st->partial.get((size_t)nchunks * W * K * 16) : nullptr;
+    // small per-wave arrays: ybar [W,R], loss_term [W]
+    char* small = (char*)st->small.get((size_t)W * (R * 16 + 8) + 64);
+    cd* ybar = (cd*)small;
+    double* loss_term = (double*)(small + (size_t)W * R * 16);
+    if (loss_sum) CK(cudaMemsetAsync(loss_sum, 0, sizeof(double), s));
+    if (status) CK(cudaMemsetAsync(status, 0, sizeof(int) * B, s));
+
+    for (int64_t b0 = 0; b0 < B; b0 += W) {
+        const int nw = (int)std::min<int64_t>(W, B - b0);
+        factor(st, s, P, nw, F, nullptr, coef + b0 * K, vals, status ? status + b0 : nullptr);
+        {
+            dim3 grid((N + 255) / 256, nw);
+            scale_rhs_kernel<<<grid, 256, 0, s>>>(N, P.d_rhs_vec, scale + b0, vb);
+            launch_check(st);
+        }
+        solve_refined(st, s, P, F, false, vals, 1, true, vb, 1, nw, vx, V, vr, vd, nw, 1, PH_FWD);
+        {
+            Span span(st, s, PH_READOUT);
+            readout_kernel<<<nw, 256, 0, s>>>(N, R, P.d_Q, vx, y + b0 * R);
+            launch_check(st);
+            if (u_out) CK(cudaMemcpyAsync(u_out + b0 * N, vx, (size_t)nw * N * 16, cudaMemcpyDeviceToDevice, s));
+        }
+        if (!adjoint) continue;
+        {
+            Span span(st, s, PH_READOUT);
+            loss_kernel<<<(nw + 127) / 128, 128, 0, s>>>(nw, R, y + b0 * R, w, ref + b0, loss_type,
+                                                         1.0 / (double)F_total, fr + b0, loss_term, ybar);
+            launch_check(st);
+            sum_kernel<<<1, 256, 0, s>>>(nw, loss_term, loss_sum);
+            launch_check(st);
+            dim3 grid((N + 255) / 256, nw);
+            cotangent_kernel<<<grid, 256, 0, s>>>(N, R, P.d_Q, ybar, vb);
+            launch_check(st);
+        }
+        solve_refined(st, s, P, F, true, vals, 1, true, vb, 1, nw, vlam, V, vr, vd, nw, 1, PH_ADJ);
+        {
+            Span span(st, s, PH_GRAD);
+            grad_kernel<KMAX><<<(unsigned)(nchunks * nw), GRAD_THREADS, 0, s>>>(
+                nnz, N, K, P.d_csc_row, P.d_csc_col, P.d_mats, vlam, vx, partial, nw);
+            launch_check(st);
+            int64_t nbk = (int64_t)nw * K;
+            grad_reduce_kernel<<<(unsigned)((nbk + 127) / 128), 128, 0, s>>>((int)nchunks, nbk, partial,
+                                                                             ct_coef + b0 * K);
+            launch_check(st);
+            readout_kernel<<<nw, 256, 0, s>>>(N, 1, P.d_rhs_vec, vlam, ct_s + b0);
+            launch_check(st);
+        }
+    }
+}
+
+}  // namespace
+
+// ============================================================================== C-ABI
+extern "C" {
+
+int jpb_create(jpb_state** out, int device) {
+    if (!out) return JPB_EINVAL;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0 || device < 0 || device >= n) return JPB_ECUDA;
+    auto st = std::make_unique<jpb_state>();
+    st->device = device;
+    if (cudaSetDevice(device) != cudaSuccess) return JPB_ECUDA;
+    if (cudaStreamCreateWithFlags(&st->stream, cudaStreamNonBlocking) != cudaSuccess) return JPB_ECUDA;
+    *out = st.release();
+    return JPB_OK;
+}
+
+void jpb_destroy(jpb_state* st) {
+    if (!st) return;
+    cudaSetDevice(st->device);
+    cudaDeviceSynchronize();
+    delete st;
+}
+
+const char* jpb_last_error(const jpb_state* st) { return st ? st->err.c_str() : "null state"; }
+
+int jpb_set_memory_budget(jpb_state* st, int64_t bytes) {
+    if (!st || bytes < 0) return JPB_EINVAL;
+    st->budget = bytes;
+    return JPB_OK;
+}
+
+int jpb_set_refinement(jpb_state* st, int steps) {
+    if (!st || steps < 0 || steps > 8) return fail(st, JPB_EINVAL, "refinement steps must be in [0, 8]");
+    st->refine = steps;
+    return JPB_OK;
+}
+
+int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, const void* indptr,
+                const void* indices_T, const void* indptr_T, const void* perm, int index_bytes,
+                int* solver_num) {
+    (void)indptr_T;   // the reference passes the CSC indptr here (Sparse.py:34); never used
+    JPB_TRY(st)
+    if (!st) throw InvalidArg("null state");
+    if (N <= 0 || N > INT32_MAX) throw InvalidArg("add_mat: N out of range");
+    if (nnz <= 0 || nnz > INT32_MAX) throw InvalidArg("add_mat: nnz out of range");
+    if (!indices || !indptr) throw InvalidArg("add_mat: null index arrays");
+    if (index_bytes != 4 && index_bytes != 8) throw InvalidArg("add_mat: index width must be 4 or 8 bytes");
+    CK(cudaSetDevice(st->device));
+    auto get = [&](const void* p, int64_t i) -> int64_t {
+        return index_bytes == 4 ? (int64_t)((const int32_t*)p)[i] : ((const int64_t*)p)[i];
+    };
+    std::vector<int64_t> ap(N + 1), ai(nnz);
+    for (int64_t i = 0; i <= N; ++i) ap[i] = get(indptr, i);
+    for (int64_t i = 0; i < nnz; ++i) ai[i] = get(indices, i);
+    if (ap[0] != 0 || ap[N] != nnz) throw InvalidArg("add_mat: indptr does not match nnz");
+    for (int64_t j = 0; j < N; ++j) {
+        if (ap[j + 1] < ap[j]) throw InvalidArg("add_mat: indptr not monotone");
+        for (int64_t e = ap[j]; e < ap[j + 1]; ++e) {
+            if (ai[e] < 0 || ai[e] >= N) throw InvalidArg("add_mat: row index out of range");
+            if (e > ap[j] && ai[e] <= ai[e - 1]) throw InvalidArg("add_mat: row indices must be strictly increasing within a column");
+        }
+    }
+    auto P = std::make_unique<Pattern>();
+    SymbolicOptions opt;
+    analyze((int)N, ap.data(), ai.data(), opt, P->S);
+    Symbolic& S = P->S;
+
+    // CSR view (exact transpose of the CSC pattern) with CSR->CSC positions
+    std::vector<int> csc_ptr(N + 1), csc_row(nnz), csc_col(nnz), csr_ptr(N + 1, 0), csr_col(nnz), csr_pos(nnz);
+    for (int64_t j = 0; j <= N; ++j) csc_ptr[j] = (int)ap[j];
+    for (int64_t j = 0; j < N; ++j)
+        for (int64_t e = ap[j]; e < ap[j + 1]; ++e) {
+            csc_row[e] = (int)ai[e];
+            csc_col[e] = (int)j;
+            csr_ptr[ai[e] + 1]++;
+        }
+    for (int64_t i = 0; i < N; ++i) csr_ptr[i + 1] += csr_ptr[i];
+    {
+        std::vector<int> pos(csr_ptr.begin(), csr_ptr.end() - 1);
+        for (int64_t j = 0; j < N; ++j)
+            for (int64_t e = ap[j]; e < ap[j + 1]; ++e) {
+                int q = pos[ai[e]]++;
+                csr_col[q] = (int)j;
+                csr_pos[q] = (int)e;
+            }
+    }
+    if (perm)
+        for (int64_t q = 0; q < nnz; ++q)
+            if (get(perm, q) != csr_pos[q]) throw InvalidArg("add_mat: `permutation` is not the CSR->CSC map of the pattern");
+    if (indices_T)
+        for (int64_t q = 0; q < nnz; ++q)
+            if (get(indices_T, q) != csr_col[q]) throw InvalidArg("add_mat: `indices_T` is not the CSR column index of the pattern");
+
+    std::vector<int> entpos(nnz);
+    for (int64_t q = 0; q < nnz; ++q) entpos[S.ent_src[q]] = (int)q;
+    std::vector<int> csr_pos_ent(nnz), csc_pos_ent(nnz);
+    for (int64_t q = 0; q < nnz; ++q) {
+        csr_pos_ent[q] = entpos[csr_pos[q]];
+        csc_pos_ent[q] = entpos[q];
+    }
+
+    std::vector<FrontDesc> fr(S.nfronts);
+    for (int f = 0; f < S.nfronts; ++f) {
+        FrontDesc& d = fr[f];
+        d.off = S.f_off[f];
+        d.entptr = S.f_entptr[f];
+        d.s = S.f_s[f];
+        d.k = S.f_k[f];
+        d.ld = S.f_ld[f];
+        d.nent = (int)(S.f_entptr[f + 1] - S.f_entptr[f]);
+        d.rowptr = S.f_rowptr[f];
+        d.voff = S.f_voff[f];
+        d.childptr = S.f_childptr[f];
+        d.nchild = S.f_childptr[f + 1] - S.f_childptr[f];
+        d.reloff = (int)std::max<int64_t>(S.f_reloff[f], 0);
+        d.parent = S.f_parent[f];
+        d.pad0 = d.pad1 = 0;
+    }
+    if (!S.relmap.empty() && (int64_t)S.relmap.size() > INT32_MAX) throw InvalidArg("add_mat: pattern too large");
+    P->levelptr = S.levelptr;
+    P->max_s = S.max_s;
+    P->d_fr = upload(fr);
+    P->d_rowidx_orig = upload(S.rowidx_orig);
+    P->d_children = upload(S.children);
+    P->d_relmap = upload(S.relmap);
+    P->d_ent_src = upload(S.ent_src);
+    P->d_ent_slot = upload(S.ent_slot);
+    P->d_levelfronts = upload(S.levelfronts);
+    P->d_csc_ptr = upload(csc_ptr);
+    P->d_csc_row = upload(csc_row);
+    P->d_csc_col = upload(csc_col);
+    P->d_csc_pos_ent = upload(csc_pos_ent);
+    P->d_csr_ptr = upload(csr_ptr);
+    P->d_csr_col = upload(csr_col);
+    P->d_csr_pos = upload(csr_pos);
+    P->d_csr_pos_ent = upload(csr_pos_ent);
+    P->sd = SymDev{P->d_fr, P->d_rowidx_orig, P->d_children, P->d_relmap, P->d_ent_src, P->d_ent_slot,
+                   S.front_slots, S.vec_slots, S.nnz, S.N};
+    // the dynamic shared memory of the solve kernels holds one front-local vector
+    size_t smem = (size_t)S.max_s * sizeof(cd);
+    if (smem > 200 * 1024) throw InvalidArg("add_mat: largest front exceeds the solve kernels' shared memory");
+    if (smem > 40 * 1024) {
+        CK(cudaFuncSetAttribute(fwd_level_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CK(cudaFuncSetAttribute(fwd_level_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CK(cudaFuncSetAttribute(bwd_level_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CK(cudaFuncSetAttribute(bwd_level_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    st->pats.push_back(std::move(P));
+    if (solver_num) *solver_num = (int)st->pats.size() - 1;
+    return JPB_OK;
+    JPB_CATCH(st)
+}
+
+int jpb_symbolic_info(const jpb_state* st, int solver_num, double* info) {
+    jpb_state* s = const_cast<jpb_state*>(st);
+    JPB_TRY(s)
+    Pattern& P = pattern(s, solver_num);
+    if (!info) throw InvalidArg("null output");
+    const Symbolic& S = P.S;
+    info[0] = S.N; info[1] = (double)S.nnz; info[2] = (double)S.nnz_lu; info[3] = S.flops;
+    info[4] = (double)S.front_slots; info[5] = S.nfronts; info[6] = S.nlevels; info[7] = S.max_s;
+    info[8] = S.max_k; info[9] = (double)S.vec_slots;
+    return JPB_OK;
+    JPB_CATCH(s)
+}
+
+int jpb_get_ordering(const jpb_state* st, int solver_num, int32_t* perm) {
+    jpb_state* s = const_cast<jpb_state*>(st);
+    JPB_TRY(s)
+    Pattern& P = pattern(s, solver_num);
+    if (!perm) throw InvalidArg("null output");
+    for (int i = 0; i < P.S.N; ++i) perm[i] = P.S.perm[i];
+    return JPB_OK;
+    JPB_CATCH(s)
+}
+
+int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const double* data,
+              const double* b, int64_t nb0, int64_t nb1, double* out, int* status) {
+    JPB_TRY(st)
+    Pattern& P = pattern(st, solver_num);
+    if (!data || !b || !out) throw InvalidArg("solve: null array");
+    ModeShape ms = decode_mode(mode, nb0, nb1);
+    CK(cudaSetDevice(st->device));
+    st->reset_timing();
+    cudaStream_t s = st->stream;
+    const int N = P.S.N;
+    const int64_t nnz = P.S.nnz;
+    const bool trans = transpose != 0;
+    // rhs chunk: bound the front-local vector workspace
+    const int64_t JC = std::min<int64_t>(ms.nrhs, 64);
+    int64_t per = (P.S.front_slots + nnz) * 16 + JC * (P.S.vec_slots + 4 * (int64_t)N) * 16 + 64;
+    int64_t W = std::max<int64_t>(1, std::min<int64_t>(ms.nsys, budget_bytes(st) / per));
+    while (W * JC > 65535) --W;
+    st->wave = (double)W;
+    cd* F = (cd*)st->F.get((size_t)W * P.S.front_slots * 16);
+    cd* dat = (cd*)st->data.get((size_t)W * nnz * 16);
+    cd* V = (cd*)st->V.get((size_t)W * JC * P.S.vec_slots * 16);
+    cd* vb = (cd*)st->vb.get((size_t)W * JC * N * 16);
+    cd* vx = (cd*)st->vx.get((size_t)W * JC * N * 16);
+    cd* vr = (cd*)st->vr.get((size_t)W * JC * N * 16);
+    cd* vd = (cd*)st->vd.get((size_t)W * JC * N * 16);
+    int* dstat = (int*)st->status.get((size_t)ms.nsys * sizeof(int));
+    CK(cudaMemsetAsync(dstat, 0, (size_t)ms.nsys * sizeof(int), s));
+    const cd* hb = (const cd*)b;
+    cd* hout = (cd*)out;
+    for (int64_t i0 = 0; i0 < ms.nsys; i0 += W) {
+        const int nw = (int)std::min<int64_t>(W, ms.nsys - i0);
+        {
+            Span span(st, s, PH_H2D);
+            CK(cudaMemcpyAsync(dat, (const cd*)data + i0 * nnz, (size_t)nw * nnz * 16, cudaMemcpyHostToDevice, s));
+        }
+        factor(st, s, P, nw, F, dat, nullptr, nullptr, dstat + i0);
+        for (int64_t j0 = 0; j0 < ms.nrhs; j0 += JC) {
+            const int nj = (int)std::min<int64_t>(JC, ms.nrhs - j0);
+            // stage rhs(b, j) densely as vb[(j * nw + b) * N]
+            int64_t sb, sj;
+            {
+                Span span(st, s, PH_H2D);
+                if (ms.rhs_sb == 0 && ms.rhs_sj == 0) {          // one shared vector (modes 0, 1)
+                    CK(cudaMemcpyAsync(vb, hb, (size_t)N * 16, cudaMemcpyHostToDevice, s));
+                    sb = 0; sj = 0;
+                } else {
+                    for (int j = 0; j < nj; ++j) {
+                        const cd* src = hb + ((j0 + j) * ms.rhs_sj + i0 * ms.rhs_sb) * N;
+                        CK(cudaMemcpyAsync(vb + (int64_t)j * nw * N, src, (size_t)nw * N * 16,
+                                           cudaMemcpyHostToDevice, s));
+                    }
+                    sb = 1; sj = nw;
+                    if (ms.rhs_sb == 0) sb = 0;
+                }
+            }
+            solve_refined(st, s, P, F, trans, dat, 1, false, vb, sb, sj, vx, V, vr, vd, nw, nj,
+                          trans ? PH_ADJ : PH_FWD);
+            {
+                Span span(st, s, PH_D2H);
+                for (int j = 0; j < nj; ++j)
+                    CK(cudaMemcpyAsync(hout + ((j0 + j) * ms.nsys + i0) * N, vx + (int64_t)j * nw * N,
+                                       (size_t)nw * N * 16, cudaMemcpyDeviceToHost, s));
+            }
+        }
+    }
+    std::vector<int> hstat(ms.nsys);
+    CK(cudaMemcpyAsync(hstat.data(), dstat, (size_t)ms.nsys * sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    int bad = 0;
+    for (int64_t i = 0; i < ms.nsys; ++i) {
+        if (status) status[i] = hstat[i];
+        bad |= hstat[i];
+    }
+    if (bad) return fail(st, JPB_ESINGULAR, "solve: matrix is singular (zero pivot block)");
+    return JPB_OK;
+    JPB_CATCH(st)
+}
+
+int jpb_matvec(jpb_state* st, int solver_num, int mode, int transpose, const double* mat,
+               const double* vec, int64_t nb0, int64_t nb1, double* out) {
+    JPB_TRY(st)
+    Pattern& P = pattern(st, solver_num);
+    if (!mat || !vec || !out) throw InvalidArg("matvec: null array");
+    ModeShape ms = decode_mode(mode, nb0, nb1);
+    CK(cudaSetDevice(st->device));
+    st->reset_timing();
+    cudaStream_t s = st->stream;
+    const int N = P.S.N;
+    const int64_t nnz = P.S.nnz;
+    const int64_t JC = std::min<int64_t>(ms.nrhs, 64);
+    int64_t per = nnz * 16 + JC * 2 * (int64_t)N * 16 + 64;
+    int64_t W = std::max<int64_t>(1, std::min<int64_t>(ms.nsys, budget_bytes(st) / per));
+    while (W * JC > 65535) --W;
+    cd* dat = (cd*)st->data.get((size_t)W * nnz * 16);
+    cd* vb = (cd*)st->vb.get((size_t)W * JC * N * 16);
+    cd* vx = (cd*)st->vx.get((size_t)W * JC * N * 16);
+    const cd* hv = (const cd*)vec;
+    cd* hout = (cd*)out;
+    for (int64_t i0 = 0; i0 < ms.nsys; i0 += W) {
+        const int nw = (int)std::min<int64_t>(W, ms.nsys - i0);
+        CK(cudaMemcpyAsync(dat, (const cd*)mat + i0 * nnz, (size_t)nw * nnz * 16, cudaMemcpyHostToDevice, s));
+        for (int64_t j0 = 0; j0 < ms.nrhs; j0 += JC) {
+            const int nj = (int)std::min<int64_t>(JC, ms.nrhs - j0);
+            int64_t sb, sj;
+            if (ms.rhs_sb == 0 && ms.rhs_sj == 0) {
+                CK(cudaMemcpyAsync(vb, hv, (size_t)N * 16, cudaMemcpyHostToDevice, s));
+                sb = 0; sj = 0;
+            } else {
+                for (int j = 0; j < nj; ++j)
+                    CK(cudaMemcpyAsync(vb + (int64_t)j * nw * N, hv + ((j0 + j) * ms.rhs_sj + i0 * ms.rhs_sb) * N,
+                                       (size_t)nw * N * 16, cudaMemcpyHostToDevice, s));
+                sb = ms.rhs_sb == 0 ? 0 : 1; sj = nw;
+            }
+            spmv(st, s, P, transpose != 0, dat, 1, false, vb, sb, sj, nullptr, 0, 0, vx, nw, nj);
+            for (int j = 0; j < nj; ++j)
+                CK(cudaMemcpyAsync(hout + ((j0 + j) * ms.nsys + i0) * N, vx + (int64_t)j * nw * N,
+                                   (size_t)nw * N * 16, cudaMemcpyDeviceToHost, s));
+        }
+    }
+    CK(cudaStreamSynchronize(s));
+    return JPB_OK;
+    JPB_CATCH(st)
+}
+
+int jpb_assemble(jpb_state* st, int64_t nnz, int K, int64_t B, const double* mats, const double* coef,
+                 double* data) {
+    JPB_TRY(st)
+    if (!st) throw InvalidArg("null state");
+    if (!mats || !coef || !data) throw InvalidArg("assemble: null array");
+    if (nnz <= 0 || B <= 0 || K <= 0 || K > KMAX) throw InvalidArg("assemble: bad sizes (K must be <= 32)");
+    CK(cudaSetDevice(st->device));
+    st->reset_timing();
+    cudaStream_t s = st->stream;
+    double* dm = (double*)st->vals.get((size_t)K * nnz * 8);
+    cd* dc = (cd*)st->small.get((size_t)B * K * 16);
+    int64_t W = std::max<int64_t>(1, std::min<int64_t>(B, budget_bytes(st) / (nnz * 16)));
+    cd* dd = (cd*)st->data.get((size_t)W * nnz * 16);
+    CK(cudaMemcpyAsync(dm, mats, (size_t)K * nnz * 8, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(dc, coef, (size_t)B * K * 16, cudaMemcpyHostToDevice, s));
+    const int bchunk = 16;
+    for (int64_t b0 = 0; b0 < B; b0 += W) {
+        const int nw = (int)std::min<int64_t>(W, B - b0);
+        dim3 grid((unsigned)((nnz + 255) / 256), (unsigned)((nw + bchunk - 1) / bchunk));
+        assemble_kernel<KMAX><<<grid, 256, (size_t)bchunk * K * 16, s>>>(nnz, K, nw, dm, dc + b0 * K, dd, bchunk);
+        launch_check(st);
+        CK(cudaMemcpyAsync((cd*)data + b0 * nnz, dd, (size_t)nw * nnz * 16, cudaMemcpyDeviceToHost, s));
+    }
+    CK(cudaStreamSynchronize(s));
+    return JPB_OK;
+    JPB_CATCH(st)
+}
+
+int jpb_register_components(jpb_state* st, int solver_num, int K, const double* mats,
+                            const double* rhs_vec, int R, const double* Q) {
+    JPB_TRY(st)
+    Pattern& P = pattern(st, solver_num);
+    if (!mats || !rhs_vec || !Q) throw InvalidArg("register_components: null array");
+    if (K <= 0 || K > KMAX) throw InvalidArg("register_components: K must be in [1, 32]");
+    if (R <= 0 || R > 4) throw InvalidArg("register_components: R must be in [1, 4]");
+    CK(cudaSetDevice(st->device));
+    const int64_t nnz = P.S.nnz;
+    const int N = P.S.N;
+    for (double** p : {&P.d_mats, &P.d_mats_f, &P.d_rhs_vec, &P.d_Q})
+        if (*p) { cudaFree(*p); *p = nullptr; }
+    P.K = 0;
+    CK(cudaMalloc(&P.d_mats, (size_t)K * nnz * 8));
+    CK(cudaMalloc(&P.d_mats_f, (size_t)K * nnz * 8));
+    CK(cudaMalloc(&P.d_rhs_vec, (size_t)N * 8));
+    CK(cudaMalloc(&P.d_Q, (size_t)R * N * 8));
+    CK(cudaMemcpy(P.d_mats, mats, (size_t)K * nnz * 8, cudaMemcpyHostToDevice));
+    std::vector<double> mf((size_t)K * nnz);
+    for (int k = 0; k < K; ++k)
+        for (int64_t q = 0; q < nnz; ++q) mf[(size_t)k * nnz + q] = mats[(size_t)k * nnz + P.S.ent_src[q]];
+    CK(cudaMemcpy(P.d_mats_f, mf.data(), (size_t)K * nnz * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(P.d_rhs_vec, rhs_vec, (size_t)N * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(P.d_Q, Q, (size_t)R * N * 8, cudaMemcpyHostToDevice));
+    P.K = K;
+    P.R = R;
+    return JPB_OK;
+    JPB_CATCH(st)
+}
+
+int jpb_eval_forward(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                     const double* rhs_scale, double* u, double* y, int* status) {
+    JPB_TRY(st)
+    Pattern& P = pattern(st, solver_num);
+    if (!coef || !rhs_scale || !y || B <= 0) throw InvalidArg("eval_forward: bad arguments");
+    if (P.K == 0) throw StateError("components not registered for this pattern (jpb_register_components)");
+    CK(cudaSetDevice(st->device));
+    st->reset_timing();
+    cudaStream_t s = st->stream;
+    const int K = P.K, R = P.R, N = P.S.N;
+    size_t bytes = (size_t)B * (K * 16 + 16 + R * 16 + 4) + 256;
+    char* stage = (char*)st->hstage.get(bytes);
+    cd* dcoef = (cd*)stage;
+    cd* dscale = dcoef + B * K;
+    cd* dy = dscale + B;
+    int* dstat = (int*)(dy + B * R);
+    cd* du = u ? (cd*)st->data.get((size_t)B * N * 16) : nullptr;
+    {
+        Span span(st, s, PH_H2D);
+        CK(cudaMemcpyAsync(dcoef, coef, (size_t)B * K * 16, cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(dscale, rhs_scale, (size_t)B * 16, cudaMemcpyHostToDevice, s));
+    }
+    eval_core(st, s, P, B, dcoef, dscale, nullptr, nullptr, 0, B, du, dy, nullptr, nullptr, nullptr,
+              nullptr, dstat, false);
+    std::vector<int> hstat(B);
+    {
+        Span span(st, s, PH_D2H);
+        CK(cudaMemcpyAsync(y, dy, (size_t)B * R * 16, cudaMemcpyDeviceToHost, s));
+        if (u) CK(cudaMemcpyAsync(u, du, (size_t)B * N * 16, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(hstat.data(), dstat, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
+    }
+    CK(cudaStreamSynchronize(s));
+    int bad = 0;
+    for (int64_t i = 0; i < B; ++i) {
+        if (status) status[i] = hstat[i];
+        bad |= hstat[i];
+    }
+    if (bad) return fail(st, JPB_ESINGULAR, "eval_forward: a system is singular (zero pivot block)");
+    return JPB_OK;
+    JPB_CATCH(st)
+}
+
+int jpb_eval_loss_grad_dev(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                           const double* rhs_scale, const double* ref, const double* w, int loss_type,
+                           int64_t F_total, double* fr, double* loss_sum, double* ct_coef, double* ct_s,
+                           int* status, void* stream) {
+    JPB_TRY(st)
+    Pattern& P = pattern(st, solver_num);
+    if (!coef || !rhs_scale || !ref || !w || !fr || !loss_sum || !ct_coef || !ct_s || B <= 0 || F_total < B)
+        throw InvalidArg("eval_loss_grad: bad arguments");
+    if (loss_type < 0 || loss_type > 3) throw InvalidArg("eval_loss_grad: unknown loss type");
+    CK(cudaSetDevice(st->device));
+    st->reset_timing();
+    cudaStream_t s = (cudaStream_t)stream;
+    cd* dy = (cd*)st->hstage.get((size_t)B * P.R * 16 + 64);
+    eval_core(st, s, P, B, (const cd*)coef, (const cd*)rhs_scale, ref, w, loss_type, F_total, nullptr, dy,
+              fr, loss_sum, (cd*)ct_coef, (cd*)ct_s, status, true);
+    return JPB_OK;
+    JPB_CATCH(st)
+}
+
+int jpb_eval_loss_grad(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                       const double* rhs_scale, const double* ref, const double* w, int loss_type,
+                       int64_t F_total, double* fr, double* loss_sum, double* ct_coef, double* ct_s,
+                       int* status) {
+    JPB_TRY(st)
+    Pattern& P = pattern(st, solver_num);
+    if (!coef || !rhs_scale || !ref || !w || !fr || !loss_sum || !ct_coef || !ct_s || B <= 0 || F_total < B)
+        throw InvalidArg("eval_loss_grad: bad arguments");
+    if (loss_type < 0 || loss_type > 3) throw InvalidArg("eval_loss_grad: unknown loss type");
+    if (P.K == 0) throw StateError("components not registered for this pattern (jpb_register_components)");
+    CK(cudaSetDevice(st->device));
+    st->reset_timing();
+    cudaStream_t s = st->stream;
+    const int K = P.K, R = P.R;
+    // device staging: coef [B,K] c, scale [B] c, y [B,R] c, ct_coef [B,K] c, ct_s [B] c,
+    // ref [B] d, fr [B] d, w [R] d, loss d, status [B] i
+    size_t nc = (size_t)B * (2 * K + 2 + R);
+    size_t bytes = nc * 16 + (size_t)B * 16 + 64 + (size_t)B * 4 + 64;
+    char* stage = (char*)st->hstage.get(bytes);
+    cd* dcoef = (cd*)stage;
+    cd* dscale = dcoef + B * K;
+    cd* dy = dscale + B;
+    cd* dct = dy + B * R;
+    cd* dcts = dct + B * K;
+    double* dref = (double*)(dcts + B);
+    double* dfr = dref + B;
+    double* dw = dfr + B;
+    double* dloss = dw + 4;
+    int* dstat = (int*)(dloss + 2);
+    {
+        Span span(st, s, PH_H2D);
+        CK(cudaMemcpyAsync(dcoef, coef, (size_t)B * K * 16, cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(dscale, rhs_scale, (size_t)B * 16, cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(dref, ref, (size_t)B * 8, cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(dw, w, (size_t)R * 8, cudaMemcpyHostToDevice, s));
+    }
+    eval_core(st, s, P, B, dcoef, dscale, dref, dw, loss_type, F_total, nullptr, dy, dfr, dloss, dct, dcts,
+              dstat, true);
+    std::vector<int> hstat(B);
+    {
+        Span span(st, s, PH_D2H);
+        CK(cudaMemcpyAsync(fr, dfr, (size_t)B * 8, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(loss_sum, dloss, 8, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(ct_coef, dct, (size_t)B * K * 16, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(ct_s, dcts, (size_t)B * 16, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(hstat.data(), dstat, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
+    }
+    CK(cudaStreamSynchronize(s));
+    int bad = 0;
+    for (int64_t i = 0; i < B; ++i) {
+        if (status) status[i] = hstat[i];
+        bad |= hstat[i];
+    }
+    if (bad) return fail(st, JPB_ESINGULAR, "eval_loss_grad: a system is singular (zero pivot block)");
+    return JPB_OK;
+    JPB_CATCH(st)
+}
+
+int jpb_last_timings(const jpb_state* st, double* t10) {
+    if (!st || !t10) return JPB_EINVAL;
+    cudaSetDevice(st->device);
+    summarise_timings(st, t10);
+    return JPB_OK;
+}
+
+int jpb_dmma_peak(jpb_state* st, double* tflops) {
+    JPB_TRY(st)
+    if (!st || !tflops) throw InvalidArg("null argument");
+    CK(cudaSetDevice(st->device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, st->device));
+    double* sink = (double*)st->small.get(64);
+    const int blocks = prop.multiProcessorCount * 4, threads = 256, iters = 20000;
+    cudaEvent_t a, b;
+    CK(cudaEventCreate(&a));
+    CK(cudaEventCreate(&b));
+    dmma_peak_kernel<<<blocks, threads, 0, st->stream>>>(1000, sink);
+    float best = 1e30f;
+    for (int rep = 0; rep < 3; ++rep) {
+        CK(cudaEventRecord(a, st->stream));
+        dmma_peak_kernel<<<blocks, threads, 0, st->stream>>>(iters, sink);
+        CK(cudaEventRecord(b, st->stream));
+        CK(cudaEventSynchronize(b));
+        float ms;
+        CK(cudaEventElapsedTime(&ms, a, b));
+        best = std::min(best, ms);
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    double flops = (double)blocks * (threads / 32) * (double)iters * 16.0 * (2.0 * 8 * 8 * 4);
+    *tflops = flops / (best * 1e-3) / 1e12;
+    return JPB_OK;
+    JPB_CATCH(st)
+}
+
+int jpb_selftest(jpb_state* st, double* max_err) {
+    JPB_TRY(st)
+    if (!st || !max_err) throw InvalidArg("null argument");
+    CK(cudaSetDevice(st->device));
+    const int lda = 37, ldb = 41;
+    std::vector<cd> A(16 * lda), B(40 * ldb);
+    unsigned seed = 12345u;
+    auto rnd = [&]() { seed = seed * 1664525u + 1013904223u; return (double)(seed >> 8) / (1 << 24) - 0.5; };
+    for (auto& v : A) v = make_double2(rnd(), rnd());
+    for (auto& v : B) v = make_double2(rnd(), rnd());
+    cd *dA = upload(A), *dB = upload(B), *dC, *dR;
+    CK(cudaMalloc(&dC, 16 * 32 * 16));
+    CK(cudaMalloc(&dR, 16 * 32 * 16));
+    double worst = 0.0;
+    const int cases[][3] = {{16, 32, 32}, {16, 32, 35}, {13, 27, 30}, {5, 3, 2}, {16, 32, 4}, {9, 17, 1}};
+    for (auto& c : cases) {
+        CK(cudaMemset(dC, 0, 16 * 32 * 16));
+        CK(cudaMemset(dR, 0, 16 * 32 * 16));
+        selftest_gemm_kernel<<<1, 32, 0, st->stream>>>(dA, lda, c[0], dB, ldb, c[1], c[2], dC, dR);
+        CK(cudaStreamSynchronize(st->stream));
+        std::vector<cd> hC(16 * 32), hR(16 * 32);
+        CK(cudaMemcpy(hC.data(), dC, 16 * 32 * 16, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(hR.data(), dR, 16 * 32 * 16, cudaMemcpyDeviceToHost));
+        double num = 0, den = 1e-300;
+        for (int i = 0; i < 16 * 32; ++i) {
+            num = std::max(num, std::max(std::fabs(hC[i].x - hR[i].x), std::fabs(hC[i].y - hR[i].y)));
+            den = std::max(den, std::max(std::fabs(hR[i].x), std::fabs(hR[i].y)));
+        }
+        worst = std::max(worst, num / den);
+    }
+    cudaFree(dA); cudaFree(dB); cudaFree(dC); cudaFree(dR);
+    *max_err = worst;
+    return JPB_OK;
+    JPB_CATCH(st)
+}
+
+}  // extern "C"

@@ -388,7 +388,7 @@ void analyze(int N, const int64_t* ap, const int64_t* ai, const SymbolicOptions&
     // ---- fronts
     const int nf = (int)st.size();
     S.nfronts = nf;
-    S.f_c0.resize(nf); S.f_k.resize(nf); S.f_s.resize(nf); S.f_off.resize(nf);
+    S.f_c0.resize(nf); S.f_k.resize(nf); S.f_s.resize(nf); S.f_off.resize(nf); S.f_ld.resize(nf);
     S.f_voff.resize(nf); S.f_rowptr.assign(nf + 1, 0); S.f_parent.assign(nf, -1);
     S.f_level.assign(nf, 0);
     std::vector<int> sn_of(N);
@@ -410,7 +410,8 @@ void analyze(int N, const int64_t* ap, const int64_t* ai, const SymbolicOptions&
         S.f_off[f] = off;
         S.f_voff[f] = (int)voff;
         const int64_t ss = S.f_s[f], kk = S.f_k[f];
-        off += ss * ss;
+        S.f_ld[f] = (int)((ss + 1) & ~(int64_t)1);
+        off += ss * S.f_ld[f];
         voff += ss;
         S.nnz_lu += kk * (2 * ss - kk);
         for (int64_t q = 0; q < kk; ++q) {
@@ -459,16 +460,11 @@ void analyze(int N, const int64_t* ap, const int64_t* ai, const SymbolicOptions&
     }
 
     // ---- child -> parent maps
-    S.f_invoff.assign(nf, -1);
     S.f_reloff.assign(nf, -1);
     {
-        int64_t ninv = 0, nrel = 0;
+        int64_t nrel = 0;
         for (int f = 0; f < nf; ++f)
-            if (S.f_parent[f] >= 0) {
-                S.f_invoff[f] = ninv; ninv += S.f_s[S.f_parent[f]];
-                S.f_reloff[f] = nrel; nrel += S.f_s[f] - S.f_k[f];
-            }
-        S.invmap.assign(ninv, -1);
+            if (S.f_parent[f] >= 0) { S.f_reloff[f] = nrel; nrel += S.f_s[f] - S.f_k[f]; }
         S.relmap.assign(nrel, -1);
         for (int f = 0; f < nf; ++f) {
             int p = S.f_parent[f];
@@ -482,14 +478,16 @@ void analyze(int N, const int64_t* ap, const int64_t* ai, const SymbolicOptions&
                 if (q >= sp || rp[q] != rc[i])
                     throw std::runtime_error("symbolic: child row missing from parent front");
                 S.relmap[S.f_reloff[f] + (i - kc)] = q;
-                S.invmap[S.f_invoff[f] + q] = i;
             }
         }
     }
+    S.rowidx_orig.resize(S.rowidx.size());
+    for (size_t i = 0; i < S.rowidx.size(); ++i) S.rowidx_orig[i] = perm[S.rowidx[i]];
 
-    // ---- A entry -> front slot
-    S.slot.resize(S.nnz);
-    std::vector<int> owner(S.nnz);
+    // ---- A entry -> (front, local slot), grouped by front
+    if (S.nnz > INT32_MAX) throw std::runtime_error("symbolic: nnz exceeds int32");
+    std::vector<int> owner(S.nnz), lslot(S.nnz);
+    S.f_entptr.assign(nf + 1, 0);
     for (int c = 0; c < N; ++c) {
         for (int64_t e = ap[c]; e < ap[c + 1]; ++e) {
             int i = pinv[ai[e]], jj = pinv[c];
@@ -502,17 +500,23 @@ void analyze(int N, const int64_t* ap, const int64_t* ai, const SymbolicOptions&
                 if (it == r + s || *it != x) throw std::runtime_error("symbolic: entry outside front");
                 return (int)(it - r);
             };
-            S.slot[e] = S.f_off[f] + (int64_t)local(i) * s + local(jj);
+            int64_t ls = (int64_t)local(i) * S.f_ld[f] + local(jj);
+            if (ls > INT32_MAX) throw std::runtime_error("symbolic: front too large");
+            lslot[e] = (int)ls;
             owner[e] = f;
+            S.f_entptr[f + 1]++;
         }
     }
-    S.entry_levelptr.assign(S.nlevels + 1, 0);
-    for (int64_t e = 0; e < S.nnz; ++e) S.entry_levelptr[S.f_level[owner[e]] + 1]++;
-    for (int l = 0; l < S.nlevels; ++l) S.entry_levelptr[l + 1] += S.entry_levelptr[l];
-    S.entry_order.resize(S.nnz);
+    for (int f = 0; f < nf; ++f) S.f_entptr[f + 1] += S.f_entptr[f];
+    S.ent_src.resize(S.nnz);
+    S.ent_slot.resize(S.nnz);
     {
-        std::vector<int64_t> pos(S.entry_levelptr.begin(), S.entry_levelptr.end() - 1);
-        for (int64_t e = 0; e < S.nnz; ++e) S.entry_order[pos[S.f_level[owner[e]]]++] = e;
+        std::vector<int64_t> pos(S.f_entptr.begin(), S.f_entptr.end() - 1);
+        for (int64_t e = 0; e < S.nnz; ++e) {
+            int64_t q = pos[owner[e]]++;
+            S.ent_src[q] = (int)e;
+            S.ent_slot[q] = lslot[e];
+        }
     }
 }
 

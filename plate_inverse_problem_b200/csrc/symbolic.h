@@ -33,19 +33,16 @@ struct Symbolic {
     std::vector<int> f_c0;       // first pivot column (permuted numbering)
     std::vector<int> f_k;        // number of pivots
     std::vector<int> f_s;        // front order (pivots + contribution rows)
-    std::vector<int64_t> f_off;  // first slot of the s*s row-major front (elements)
+    std::vector<int> f_ld;       // leading dimension of the row-major front (s rounded up to even)
+    std::vector<int64_t> f_off;  // first slot of the s x ld row-major front (elements)
     std::vector<int> f_voff;     // first slot of the front-local vector (length s)
     std::vector<int> f_rowptr;   // [nfronts+1] into rowidx
     std::vector<int> rowidx;     // permuted global indices, first k of a front = its pivots
+    std::vector<int> rowidx_orig; // perm[rowidx]: the same rows in the caller's numbering
     std::vector<int> f_parent;   // parent front or -1
     std::vector<int> f_level;    // 0 = leaves
     std::vector<int> f_childptr; // [nfronts+1] into children
     std::vector<int> children;   // child front ids, ascending
-    // for child c: inv map of length s_parent, f_invoff[c] into invmap (-1 when root):
-    // invmap[f_invoff[c] + i_parent] = local row of child c that lands on parent row
-    // i_parent, or -1.
-    std::vector<int64_t> f_invoff;
-    std::vector<int> invmap;
     // for child c: relmap[f_reloff[c] + (i - k_c)] = parent-local row of child row i >= k_c
     std::vector<int64_t> f_reloff;
     std::vector<int> relmap;
@@ -54,14 +51,14 @@ struct Symbolic {
     std::vector<int> levelptr;    // [nlevels+1] into levelfronts
     std::vector<int> levelfronts; // fronts of a level, largest first
 
-    // slot[e] for every entry e of A in the canonical CSC order handed to add_mat
-    std::vector<int64_t> slot;
-    // entries grouped by the level of the front that owns them: e = entry_order[q],
-    // q in [entry_levelptr[l], entry_levelptr[l+1])
-    std::vector<int64_t> entry_order;
-    std::vector<int64_t> entry_levelptr;
+    // entries of A grouped by the front that owns them: for q in [f_entptr[f], f_entptr[f+1])
+    // entry ent_src[q] (position in the canonical CSC order handed to add_mat) lands on
+    // front-local slot ent_slot[q] = i_local * ld + j_local.
+    std::vector<int64_t> f_entptr;
+    std::vector<int> ent_src;
+    std::vector<int> ent_slot;
 
-    int64_t front_slots = 0;   // sum s*s
+    int64_t front_slots = 0;   // sum s*ld
     int64_t vec_slots = 0;     // sum s
     int64_t nnz_lu = 0;        // entries of L+U (diagonal counted once)
     double flops = 0;          // real flops of one numeric factorisation (complex fma = 8)
