@@ -135,6 +135,20 @@ int jpb_dmma_peak(jpb_state* st, double* tflops);
 /* self test of the dense-front kernels against scalar device loops; returns max rel err */
 int jpb_selftest(jpb_state* st, double* max_err);
 
+/* ---- host-only view of the symbolic analysis (no CUDA device needed) ------------------
+ * Used by the CPU test-suite to replay the multifrontal schedule in numpy and by tools
+ * that want the ordering / fill statistics.  sizes: [0]=nfronts, [1]=len(rowidx),
+ * [2]=len(relmap), [3]=nnz, [4]=nlevels, [5]=front_slots, [6]=nnz_lu, [7]=N. */
+typedef struct jpb_host_symbolic jpb_host_symbolic;
+int jpb_host_analyze(int64_t N, int64_t nnz, const void* indices, const void* indptr,
+                     int index_bytes, jpb_host_symbolic** out, char* errbuf, int errlen);
+int jpb_host_sizes(const jpb_host_symbolic* h, int64_t* sizes8, double* flops);
+int jpb_host_export(const jpb_host_symbolic* h, int32_t* perm, int32_t* f_s, int32_t* f_k,
+                    int32_t* f_ld, int64_t* f_off, int32_t* f_rowptr, int32_t* rowidx,
+                    int32_t* f_parent, int32_t* f_level, int64_t* f_reloff, int32_t* relmap,
+                    int64_t* f_entptr, int32_t* ent_src, int32_t* ent_slot);
+void jpb_host_free(jpb_host_symbolic* h);
+
 #ifdef __cplusplus
 }
 #endif

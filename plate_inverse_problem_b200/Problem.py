@@ -1,0 +1,255 @@
+"""`Problem`: the reference's problem object (`/root/reference/source/jax_plate/Problem.py`)
+restricted to the live (unsymmetric, accelerometer) path, with the per-frequency body of
+`_solve` (`Problem.py:432-477`), the losses (`:948-975`) and their reverse-mode derivative
+executed by the fused CUDA path (`jpb_eval_forward`, `jpb_eval_loss_grad`).
+
+What is kept from the reference interface: `Problem(geometry, material, accelerometer,
+ref_fr)`, `.getFRFunction()` -> `f(freqs, params) -> fr[F]`, `.solveForward(freqs, params)`,
+`.getLossFunction(frequencies, reference_fr, func_type, scaling_params)`.  What differs:
+* FreeFem++ is not available, so `geometry` carries the output tuple of
+  `load_matrices_unsymm` (`pyFFInterface.py:503-509`) -- e.g. from `synthetic.make_plate` --
+  instead of an .edp file name;
+* the callable returned by `getLossFunction` also has `.value_and_grad(params)` (the
+  reference obtains it with `jax.value_and_grad`, `Optimizers.py:232,258`);
+* with `torch.distributed` initialised the frequency list is sharded over the ranks and the
+  loss / gradient partials are summed with ONE all-reduce (NCCL over NVLink).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Callable
+
+import numpy as np
+
+from . import _lib
+from .Material import Material, coefficients_and_jacobian
+from .Sparse import find_permutation, symbolic_indices
+
+
+@dataclass
+class AccelerometerParams:
+    """`Accelerometer.py:8-33`."""
+    mass: float
+    radius: float
+    height: float
+    effective_height: float
+    transverse_sensitivity: float
+
+
+AP1030 = AccelerometerParams(0.0017, 0.0038, 0.0087, 0.5, 0.03)   # accelerometers/AP1030.json
+
+
+@dataclass
+class Geometry:
+    """Stand-in for `Geometry.py`: plate thickness + the FreeFEM output tuple."""
+    height: float
+    matrices: tuple   # (mats[26] COO, rhs_vec, interp_mat, interp_mat_Lh, Lh, Mh, mesh, interp_Wx, interp_Wy)
+
+
+def union_pattern_and_align(mats, N: int):
+    """`Problem.py:317-345` with int64 keys: union of the component patterns in canonical
+    (CSC) order and every component's data aligned to it.
+    Returns nz_idx [nnz,2], (mat, mat_T, coo_indices, perm) of `symbolic_indices`, mats [K,nnz]."""
+    def unwind(m):
+        return m.row.astype(np.int64) + np.int64(N) * m.col.astype(np.int64)
+
+    mats = [m.tocoo() for m in mats]
+    pattern = np.array([], dtype=np.int64)
+    for m in mats:
+        pattern = np.union1d(pattern, unwind(m))
+    rows, cols = pattern % N, pattern // N
+    nz_idx = np.vstack((rows, cols)).T
+    sym = symbolic_indices(N, nz_idx)
+    coo_indices = sym[2]
+    perm = find_permutation(nz_idx, coo_indices, N)
+    out = np.zeros((len(mats), rows.size), dtype=np.float64)
+    for i, m in enumerate(mats):
+        idx = unwind(m)
+        order = np.argsort(idx)
+        mask = np.isin(pattern, idx[order], assume_unique=True)
+        data = np.zeros(rows.size, dtype=np.float64)
+        data[mask] = m.data[order]
+        out[i] = data[perm]
+    return nz_idx, sym, out
+
+
+class Problem:
+    def __init__(self, geometry: Geometry, material: Material, accelerometer: AccelerometerParams,
+                 ref_fr=None, *, cpu: int = 0, device: int = None, refinement: int = 1):
+        import os
+        self.geometry, self.material, self.accelerometer = geometry, material, accelerometer
+        self.reference_fr = ref_fr
+        self.n_cpu = cpu    # accepted for interface parity; the batch loop runs on the GPU
+        self.rho = material.density
+        self.parameters = material.get_parameters()
+        ff = geometry.matrices
+        ff = ff.as_tuple() if hasattr(ff, "as_tuple") else ff
+        mats = list(ff[0])
+        self.mat_size = N = mats[0].shape[0]
+        nz_idx, (mat, mat_T, coo_indices, perm), self.mats = union_pattern_and_align(mats, N)
+        self.sparsity = nz_idx.shape[0] / N ** 2
+        self.nz_mask = (coo_indices[:, 0], coo_indices[:, 1])
+        self.vec = np.ascontiguousarray(ff[1], dtype=np.float64)
+        self.interp_mat, self.interp_mat_Lh = np.asarray(ff[2]), np.asarray(ff[3])
+        self.Lh_size, self.Mh_size, self.mesh = ff[4], ff[5], ff[6]
+        self.interp_mat_Wx, self.interp_mat_Wy = np.asarray(ff[7]), np.asarray(ff[8])
+        acc, h = accelerometer, geometry.height
+        rho_corr = acc.mass / (np.pi * acc.radius ** 2) / acc.height        # Problem.py:356-374
+        self.I0 = h * self.rho
+        self.I0Corr = acc.height * rho_corr
+        self.I2 = self.rho * h ** 3 / 12
+        self.I2Corr = rho_corr / 3 * ((h / 2 + acc.height) ** 3 - h ** 3 / 8)
+        self.transform = material.get_ABD_transform(h)
+        # read-out rows (row means of the dense interpolation matrices, Problem.py:454-462)
+        Lh = self.Lh_size
+        Q = np.zeros((3, N))
+        mL = self.interp_mat_Lh.mean(axis=0)
+        hh = acc.effective_height * acc.height
+        Q[0, :Lh] = mL
+        Q[0, 2 * Lh:] = -hh * self.interp_mat_Wx.mean(axis=0)
+        Q[1, Lh:2 * Lh] = mL
+        Q[1, 2 * Lh:] = -hh * self.interp_mat_Wy.mean(axis=0)
+        Q[2, 2 * Lh:] = self.interp_mat.mean(axis=0)
+        self.Q = Q
+        ts = acc.transverse_sensitivity
+        self.weights = np.array([ts ** 2, ts ** 2, 1.0])
+        # native state
+        if device is None:
+            device = int(os.environ.get("LOCAL_RANK", "0"))
+        self._st = st = _lib.State(device)
+        idx = np.ascontiguousarray(mat.indices)
+        iptr = np.ascontiguousarray(mat.indptr.astype(idx.dtype))
+        idxT = np.ascontiguousarray(mat_T.indices.astype(idx.dtype))
+        permc = np.ascontiguousarray(perm.astype(idx.dtype))
+        num = _lib.C.c_int(-1)
+        st.check(st.lib.jpb_add_mat(st.h, N, idx.size, _lib.ptr(idx), _lib.ptr(iptr), _lib.ptr(idxT),
+                                    _lib.ptr(iptr), _lib.ptr(permc), idx.dtype.itemsize, _lib.C.byref(num)))
+        self.solver_num = num.value
+        st.check(st.lib.jpb_set_refinement(st.h, int(refinement)))
+        self.mats = np.ascontiguousarray(self.mats)
+        st.check(st.lib.jpb_register_components(st.h, self.solver_num, self.mats.shape[0],
+                                                _lib.ptr(self.mats), _lib.ptr(self.vec), 3,
+                                                _lib.ptr(np.ascontiguousarray(Q))))
+
+    # ---- helpers -------------------------------------------------------------------------
+    @property
+    def inertia(self):
+        return (self.I0, self.I0Corr, self.I2, self.I2Corr)
+
+    def coefficients(self, freqs, params, with_jacobian=False):
+        return coefficients_and_jacobian(self.transform, params, freqs, self.inertia, with_jacobian)
+
+    def timings(self):
+        return self._st.timings()
+
+    def symbolic_info(self):
+        return self._st.symbolic_info(self.solver_num)
+
+    @staticmethod
+    def _shard(n):
+        """Contiguous block of [0, n) owned by this rank."""
+        try:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                r, w = dist.get_rank(), dist.get_world_size()
+                lo, hi = (n * r) // w, (n * (r + 1)) // w
+                return lo, hi, dist
+        except ImportError:
+            pass
+        return 0, n, None
+
+    # ---- forward -------------------------------------------------------------------------
+    def _forward_raw(self, freqs, params, return_u=False):
+        freqs = np.atleast_1d(np.asarray(freqs, dtype=np.float64))
+        coef, s, _, _ = self.coefficients(freqs, params)
+        F = freqs.size
+        coef, s = np.ascontiguousarray(coef), np.ascontiguousarray(s)
+        y = np.zeros((F, 3), dtype=np.complex128)
+        u = np.zeros((F, self.mat_size), dtype=np.complex128) if return_u else None
+        st = self._st
+        st.check(st.lib.jpb_eval_forward(st.h, self.solver_num, F, _lib.ptr(coef), _lib.ptr(s),
+                                         _lib.ptr(u), _lib.ptr(y), None))
+        fr = np.sqrt((self.weights[None, :] * np.abs(y) ** 2).sum(axis=1))
+        return (fr, y, u) if return_u else (fr, y)
+
+    def getFRFunction(self) -> Callable:
+        """`Problem.py:377-518`: f(freqs[F], params[P]) -> fr[F] (real amplitudes)."""
+        def fr_function(freqs, params):
+            freqs = np.atleast_1d(np.asarray(freqs, dtype=np.float64))
+            lo, hi, dist = self._shard(freqs.size)
+            fr = np.zeros(freqs.size)
+            if hi > lo:
+                fr[lo:hi] = self._forward_raw(freqs[lo:hi], params)[0]
+            if dist is not None:
+                import torch
+                dev = torch.device("cuda", self._st.device) if dist.get_backend() == "nccl" else "cpu"
+                t = torch.from_numpy(fr).to(dev)
+                dist.all_reduce(t)
+                fr = t.cpu().numpy()
+            return fr
+        return fr_function
+
+    def solveForward(self, freqs, params=None):
+        """`Problem.py:611-639`."""
+        if params is None:
+            params = self.parameters
+        return self.getFRFunction()(freqs, np.asarray(params, dtype=np.float64))
+
+    # ---- loss + gradient -----------------------------------------------------------------
+    def getLossFunction(self, frequencies, reference_fr, func_type: str, scaling_params=None):
+        """`Problem.py:933-980`.  Returns `loss(params) -> float` with the extra method
+        `loss.value_and_grad(params) -> (float, grad[P])`."""
+        frequencies = np.atleast_1d(np.asarray(frequencies, dtype=np.float64))
+        reference_fr = np.asarray(reference_fr, dtype=np.float64)
+        assert frequencies.shape[0] == reference_fr.shape[0]
+        if func_type not in _lib.LOSS_TYPES:
+            raise ValueError(f'Function type "{func_type}" is not supported!')
+        scaling = 1.0 if scaling_params is None else np.array(scaling_params, dtype=np.float64)
+        F = frequencies.size
+        ltype = _lib.LOSS_TYPES[func_type]
+
+        def value_and_grad(params):
+            p = np.asarray(params, dtype=np.float64) * scaling
+            lo, hi, dist = self._shard(F)
+            nloc = hi - lo
+            acc = np.zeros(1 + p.size)
+            if nloc > 0:
+                coef, s, dc, ds = self.coefficients(frequencies[lo:hi], p, with_jacobian=True)
+                coef, s = np.ascontiguousarray(coef), np.ascontiguousarray(s)
+                ref = np.ascontiguousarray(reference_fr[lo:hi])
+                fr, loss_sum = np.zeros(nloc), np.zeros(1)
+                ct = np.zeros((nloc, coef.shape[1]), dtype=np.complex128)
+                cts = np.zeros(nloc, dtype=np.complex128)
+                st = self._st
+                st.check(st.lib.jpb_eval_loss_grad(st.h, self.solver_num, nloc, _lib.ptr(coef), _lib.ptr(s),
+                                                   _lib.ptr(ref), _lib.ptr(self.weights), ltype, F,
+                                                   _lib.ptr(fr), _lib.ptr(loss_sum), _lib.ptr(ct),
+                                                   _lib.ptr(cts), None))
+                acc[0] = loss_sum[0] / F
+                # chain rule through the coefficient functions
+                acc[1:] = np.real(np.einsum("fk,fkp->p", ct, dc) + np.einsum("f,fp->p", cts, ds))
+                value_and_grad.last_fr = fr
+            if dist is not None:
+                import torch
+                dev = torch.device("cuda", self._st.device) if dist.get_backend() == "nccl" else "cpu"
+                t = torch.from_numpy(acc).to(dev)
+                dist.all_reduce(t)          # the single collective of the path
+                acc = t.cpu().numpy()
+            return float(acc[0]), acc[1:] * scaling
+
+        fr_function = self.getFRFunction()
+
+        def loss(params):
+            fr = fr_function(frequencies, np.asarray(params, dtype=np.float64) * scaling)
+            if func_type == "MSE":
+                return float(np.mean(np.abs(fr - reference_fr) ** 2))
+            if func_type == "RMSE":
+                return float(np.mean(np.abs((fr - reference_fr) / reference_fr) ** 2))
+            if func_type == "MSE_AFC":
+                return float(np.mean((np.abs(fr) - np.abs(reference_fr)) ** 2))
+            return float(np.mean((np.log(np.abs(fr)) - np.log(np.abs(reference_fr))) ** 2))
+
+        loss.value_and_grad = value_and_grad
+        loss.grad = lambda params: value_and_grad(params)[1]
+        loss.__name__ = func_type + "Loss"
+        return loss

@@ -23,6 +23,7 @@ EXPORTED_SYMBOLS = (
     "jpb_add_mat", "jpb_symbolic_info", "jpb_get_ordering", "jpb_solve", "jpb_matvec",
     "jpb_assemble", "jpb_register_components", "jpb_eval_forward", "jpb_eval_loss_grad",
     "jpb_eval_loss_grad_dev", "jpb_last_timings", "jpb_dmma_peak", "jpb_selftest",
+    "jpb_host_analyze", "jpb_host_sizes", "jpb_host_export", "jpb_host_free",
 )
 
 _lib = None
@@ -59,8 +60,13 @@ def load_library() -> C.CDLL:
     lib.jpb_last_timings.argtypes = [vp, dp]
     lib.jpb_dmma_peak.argtypes = [vp, dp]
     lib.jpb_selftest.argtypes = [vp, dp]
+    lib.jpb_host_analyze.argtypes = [i64, i64, dp, dp, i32, C.POINTER(vp), C.c_char_p, i32]
+    lib.jpb_host_sizes.argtypes = [vp, dp, dp]
+    lib.jpb_host_export.argtypes = [vp] + [dp] * 14
+    lib.jpb_host_free.argtypes = [vp]
+    lib.jpb_host_free.restype = None
     for name in EXPORTED_SYMBOLS:
-        if name not in ("jpb_destroy", "jpb_last_error"):
+        if name not in ("jpb_destroy", "jpb_last_error", "jpb_host_free"):
             getattr(lib, name).restype = i32
     _lib = lib
     return lib
@@ -117,3 +123,35 @@ class State:
         keys = ("N", "nnz", "nnz_lu", "flops", "front_slots", "nfronts", "nlevels", "max_front",
                 "max_pivots", "vec_slots")
         return dict(zip(keys, t.tolist()))
+
+
+def host_symbolic(N: int, indices: np.ndarray, indptr: np.ndarray) -> dict:
+    """Run the symbolic analysis on the host (no GPU needed) and return its arrays."""
+    lib = load_library()
+    indices = np.ascontiguousarray(indices)
+    indptr = np.ascontiguousarray(indptr, dtype=indices.dtype)
+    h = C.c_void_p()
+    err = C.create_string_buffer(512)
+    rc = lib.jpb_host_analyze(int(N), int(indices.size), ptr(indices), ptr(indptr),
+                              indices.dtype.itemsize, C.byref(h), err, 512)
+    if rc != JPB_OK:
+        raise RuntimeError(err.value.decode())
+    try:
+        z = np.zeros(8, dtype=np.int64)
+        fl = np.zeros(1)
+        lib.jpb_host_sizes(h, ptr(z), ptr(fl))
+        nf, nrow, nrel, nnz = (int(v) for v in z[:4])
+        i32, i64 = np.int32, np.int64
+        out = dict(perm=np.zeros(N, i32), f_s=np.zeros(nf, i32), f_k=np.zeros(nf, i32),
+                   f_ld=np.zeros(nf, i32), f_off=np.zeros(nf, i64), f_rowptr=np.zeros(nf + 1, i32),
+                   rowidx=np.zeros(nrow, i32), f_parent=np.zeros(nf, i32), f_level=np.zeros(nf, i32),
+                   f_reloff=np.zeros(nf, i64), relmap=np.zeros(max(nrel, 1), i32),
+                   f_entptr=np.zeros(nf + 1, i64), ent_src=np.zeros(nnz, i32), ent_slot=np.zeros(nnz, i32))
+        lib.jpb_host_export(h, *[ptr(out[k]) for k in ("perm", "f_s", "f_k", "f_ld", "f_off", "f_rowptr",
+                                                        "rowidx", "f_parent", "f_level", "f_reloff",
+                                                        "relmap", "f_entptr", "ent_src", "ent_slot")])
+        out.update(nfronts=nf, nlevels=int(z[4]), front_slots=int(z[5]), nnz_lu=int(z[6]), N=int(z[7]),
+                   flops=float(fl[0]), nnz=nnz)
+        return out
+    finally:
+        lib.jpb_host_free(h)

@@ -945,4 +945,55 @@ int jpb_selftest(jpb_state* st, double* max_err) {
     JPB_CATCH(st)
 }
 
+struct jpb_host_symbolic {
+    Symbolic S;
+};
+
+int jpb_host_analyze(int64_t N, int64_t nnz, const void* indices, const void* indptr, int index_bytes,
+                     jpb_host_symbolic** out, char* errbuf, int errlen) {
+    try {
+        if (!out || !indices || !indptr || N <= 0 || nnz <= 0 || (index_bytes != 4 && index_bytes != 8))
+            throw std::runtime_error("host_analyze: bad arguments");
+        auto get = [&](const void* p, int64_t i) -> int64_t {
+            return index_bytes == 4 ? (int64_t)((const int32_t*)p)[i] : ((const int64_t*)p)[i];
+        };
+        std::vector<int64_t> ap(N + 1), ai(nnz);
+        for (int64_t i = 0; i <= N; ++i) ap[i] = get(indptr, i);
+        for (int64_t i = 0; i < nnz; ++i) ai[i] = get(indices, i);
+        if (ap[0] != 0 || ap[N] != nnz) throw std::runtime_error("host_analyze: indptr does not match nnz");
+        auto h = std::make_unique<jpb_host_symbolic>();
+        analyze((int)N, ap.data(), ai.data(), SymbolicOptions(), h->S);
+        *out = h.release();
+        return JPB_OK;
+    } catch (const std::exception& e) {
+        if (errbuf && errlen > 0) snprintf(errbuf, errlen, "%s", e.what());
+        return JPB_EINVAL;
+    }
+}
+
+int jpb_host_sizes(const jpb_host_symbolic* h, int64_t* z, double* flops) {
+    if (!h || !z) return JPB_EINVAL;
+    const Symbolic& S = h->S;
+    z[0] = S.nfronts; z[1] = (int64_t)S.rowidx.size(); z[2] = (int64_t)S.relmap.size(); z[3] = S.nnz;
+    z[4] = S.nlevels; z[5] = S.front_slots; z[6] = S.nnz_lu; z[7] = S.N;
+    if (flops) *flops = S.flops;
+    return JPB_OK;
+}
+
+int jpb_host_export(const jpb_host_symbolic* h, int32_t* perm, int32_t* f_s, int32_t* f_k, int32_t* f_ld,
+                    int64_t* f_off, int32_t* f_rowptr, int32_t* rowidx, int32_t* f_parent,
+                    int32_t* f_level, int64_t* f_reloff, int32_t* relmap, int64_t* f_entptr,
+                    int32_t* ent_src, int32_t* ent_slot) {
+    if (!h) return JPB_EINVAL;
+    const Symbolic& S = h->S;
+    auto cp = [](auto* dst, const auto& v) { if (dst) std::copy(v.begin(), v.end(), dst); };
+    cp(perm, S.perm); cp(f_s, S.f_s); cp(f_k, S.f_k); cp(f_ld, S.f_ld); cp(f_off, S.f_off);
+    cp(f_rowptr, S.f_rowptr); cp(rowidx, S.rowidx); cp(f_parent, S.f_parent); cp(f_level, S.f_level);
+    cp(f_reloff, S.f_reloff); cp(relmap, S.relmap); cp(f_entptr, S.f_entptr); cp(ent_src, S.ent_src);
+    cp(ent_slot, S.ent_slot);
+    return JPB_OK;
+}
+
+void jpb_host_free(jpb_host_symbolic* h) { delete h; }
+
 }  // extern "C"
