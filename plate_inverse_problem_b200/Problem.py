@@ -126,6 +126,7 @@ class Problem:
                                     _lib.ptr(iptr), _lib.ptr(permc), idx.dtype.itemsize, _lib.C.byref(num)))
         self.solver_num = num.value
         st.check(st.lib.jpb_set_refinement(st.h, int(refinement)))
+        self._refinement = int(refinement)
         self.mats = np.ascontiguousarray(self.mats)
         st.check(st.lib.jpb_register_components(st.h, self.solver_num, self.mats.shape[0],
                                                 _lib.ptr(self.mats), _lib.ptr(self.vec), 3,

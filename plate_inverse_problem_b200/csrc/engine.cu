@@ -5,6 +5,7 @@
 #include "../../include/jax_plate_b200.h"
 
 #include <algorithm>
+#include <array>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -81,6 +82,8 @@ T* upload(const std::vector<T>& v) {
 struct Pattern {
     Symbolic S;
     std::vector<int> levelptr;
+    // fronts of a level are sorted by order, largest first; cls[l] = {#big, #mid} (rest small)
+    std::vector<std::array<int, 2>> cls;
     // symbolic data on the device
     FrontDesc* d_fr = nullptr;
     int *d_rowidx_orig = nullptr, *d_children = nullptr, *d_relmap = nullptr, *d_ent_src = nullptr,
@@ -212,51 +215,67 @@ void launch_check(jpb_state* st) {
     if (e != cudaSuccess) throw CudaError(std::string("kernel launch failed: ") + cudaGetErrorString(e));
 }
 
+// size classes of fronts: CTA width follows the front order
+constexpr int FRONT_BIG = 128, FRONT_MID = 48;
+constexpr int NT_BIG = 256, NT_MID = 128, NT_SMALL = 64;
+
+template <class Launch>
+void for_each_class(jpb_state* st, Pattern& P, int l, int64_t mult, Launch&& launch) {
+    const int n = P.levelptr[l + 1] - P.levelptr[l];
+    const int nbig = P.cls[l][0], nmid = P.cls[l][1], nsmall = n - nbig - nmid;
+    const int* lf = P.d_levelfronts + P.levelptr[l];
+    const int cnt[3] = {nbig, nmid, nsmall};
+    const int off[3] = {0, nbig, nbig + nmid};
+    for (int c = 0; c < 3; ++c) {
+        if (!cnt[c]) continue;
+        int64_t grid = (int64_t)cnt[c] * mult;
+        if (grid > 0x7fffffff) throw InvalidArg("wave too large for one launch");
+        launch(c, lf + off[c], (unsigned)grid);
+        launch_check(st);
+    }
+}
+
 // numeric factorisation of `nsys` systems into F
 void factor(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* F, const cd* data, const cd* coef,
             cd* vals, int* status) {
     Span span(st, s, PH_FACTOR);
     const bool fused = data == nullptr;
     for (int l = 0; l < P.S.nlevels; ++l) {
-        int nf = P.levelptr[l + 1] - P.levelptr[l];
-        int64_t grid = (int64_t)nf * nsys;
-        if (grid > 0x7fffffff) throw InvalidArg("wave too large for one launch");
-        const int* lf = P.d_levelfronts + P.levelptr[l];
-        if (fused)
-            factor_level_kernel<true><<<(unsigned)grid, FACTOR_THREADS, 0, s>>>(
-                P.sd, lf, nsys, F, nullptr, coef, P.d_mats_f, P.K, vals, status);
-        else
-            factor_level_kernel<false><<<(unsigned)grid, FACTOR_THREADS, 0, s>>>(
-                P.sd, lf, nsys, F, data, nullptr, nullptr, 0, nullptr, status);
-        launch_check(st);
+        for_each_class(st, P, l, nsys, [&](int c, const int* lf, unsigned grid) {
+#define JPB_FACTOR(NT)                                                                              \
+    if (fused)                                                                                      \
+        factor_level_kernel<true, NT><<<grid, NT, 0, s>>>(P.sd, lf, nsys, F, nullptr, coef, P.d_mats_f, \
+                                                          P.K, vals, status);                       \
+    else                                                                                            \
+        factor_level_kernel<false, NT><<<grid, NT, 0, s>>>(P.sd, lf, nsys, F, data, nullptr, nullptr, 0, \
+                                                           nullptr, status);
+            if (c == 0) { JPB_FACTOR(NT_BIG) } else if (c == 1) { JPB_FACTOR(NT_MID) } else { JPB_FACTOR(NT_SMALL) }
+#undef JPB_FACTOR
+        });
     }
 }
 
 // x(b, j) = A_b^-1 rhs(b, j)  (or A_b^-T)
 void tri_solve(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool trans, VecView vv, int phase) {
     Span span(st, s, phase);
-    size_t smem = (size_t)P.max_s * sizeof(cd);
-    for (int l = 0; l < P.S.nlevels; ++l) {
-        int nf = P.levelptr[l + 1] - P.levelptr[l];
-        int64_t grid = (int64_t)nf * vv.nsys * vv.nrhs;
-        if (grid > 0x7fffffff) throw InvalidArg("wave too large for one launch");
-        const int* lf = P.d_levelfronts + P.levelptr[l];
-        if (trans)
-            fwd_level_kernel<true><<<(unsigned)grid, SOLVE_THREADS, smem, s>>>(P.sd, lf, F, vv);
-        else
-            fwd_level_kernel<false><<<(unsigned)grid, SOLVE_THREADS, smem, s>>>(P.sd, lf, F, vv);
-        launch_check(st);
-    }
-    for (int l = P.S.nlevels - 1; l >= 0; --l) {
-        int nf = P.levelptr[l + 1] - P.levelptr[l];
-        int64_t grid = (int64_t)nf * vv.nsys * vv.nrhs;
-        const int* lf = P.d_levelfronts + P.levelptr[l];
-        if (trans)
-            bwd_level_kernel<true><<<(unsigned)grid, SOLVE_THREADS, smem, s>>>(P.sd, lf, F, vv);
-        else
-            bwd_level_kernel<false><<<(unsigned)grid, SOLVE_THREADS, smem, s>>>(P.sd, lf, F, vv);
-        launch_check(st);
-    }
+    const size_t smem = (size_t)P.max_s * sizeof(cd);
+    const int64_t mult = (int64_t)vv.nsys * vv.nrhs;
+#define JPB_SOLVE(KERNEL, NT)                                                      \
+    if (trans) KERNEL<true, NT><<<grid, NT, smem, s>>>(P.sd, lf, F, vv);           \
+    else KERNEL<false, NT><<<grid, NT, smem, s>>>(P.sd, lf, F, vv);
+    for (int l = 0; l < P.S.nlevels; ++l)
+        for_each_class(st, P, l, mult, [&](int c, const int* lf, unsigned grid) {
+            if (c == 0) { JPB_SOLVE(fwd_level_kernel, NT_BIG) }
+            else if (c == 1) { JPB_SOLVE(fwd_level_kernel, NT_MID) }
+            else { JPB_SOLVE(fwd_level_kernel, NT_SMALL) }
+        });
+    for (int l = P.S.nlevels - 1; l >= 0; --l)
+        for_each_class(st, P, l, mult, [&](int c, const int* lf, unsigned grid) {
+            if (c == 0) { JPB_SOLVE(bwd_level_kernel, NT_BIG) }
+            else if (c == 1) { JPB_SOLVE(bwd_level_kernel, NT_MID) }
+            else { JPB_SOLVE(bwd_level_kernel, NT_SMALL) }
+        });
+#undef JPB_SOLVE
 }
 
 // y(b,j) = [rhs(b,j) -] op(A_b) x(b,j)
@@ -327,7 +346,7 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
     const int N = P.S.N;
     const int64_t nnz = P.S.nnz;
     const int K = P.K, R = P.R;
-    const int64_t nchunks = (nnz + GRAD_THREADS * GRAD_PER_THREAD - 1) / (GRAD_THREADS * GRAD_PER_THREAD);
+    const int64_t nchunks = (nnz + GRAD_CHUNK - 1) / GRAD_CHUNK;
     // per-system workspace bytes
     int64_t per = (P.S.front_slots + nnz + P.S.vec_slots + 5 * (int64_t)N) * 16 + nchunks * K * 16 + 256;
     int64_t W = std::max<int64_t>(1, std::min<int64_t>(B, budget_bytes(st) / per));
@@ -379,8 +398,9 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
         solve_refined(st, s, P, F, true, vals, 1, true, vb, 1, nw, vlam, V, vr, vd, nw, 1, PH_ADJ);
         {
             Span span(st, s, PH_GRAD);
-            grad_kernel<KMAX><<<(unsigned)(nchunks * nw), GRAD_THREADS, 0, s>>>(
-                nnz, N, K, P.d_csc_row, P.d_csc_col, P.d_mats, vlam, vx, partial, nw);
+            const int ngroups = (nw + GRAD_SYS - 1) / GRAD_SYS;
+            grad_kernel<<<(unsigned)(nchunks * ngroups), GRAD_THREADS, GRAD_SMEM, s>>>(
+                nnz, N, K, P.d_csc_row, P.d_csc_col, P.d_mats, vlam, vx, partial, nw, ngroups);
             launch_check(st);
             int64_t nbk = (int64_t)nw * K;
             grad_reduce_kernel<<<(unsigned)((nbk + 127) / 128), 128, 0, s>>>((int)nchunks, nbk, partial,
@@ -407,6 +427,9 @@ int jpb_create(jpb_state** out, int device) {
     st->device = device;
     if (cudaSetDevice(device) != cudaSuccess) return JPB_ECUDA;
     if (cudaStreamCreateWithFlags(&st->stream, cudaStreamNonBlocking) != cudaSuccess) return JPB_ECUDA;
+    if (cudaFuncSetAttribute(grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GRAD_SMEM) !=
+        cudaSuccess)
+        return JPB_ECUDA;
     *out = st.release();
     return JPB_OK;
 }
@@ -516,6 +539,16 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
     if (!S.relmap.empty() && (int64_t)S.relmap.size() > INT32_MAX) throw InvalidArg("add_mat: pattern too large");
     P->levelptr = S.levelptr;
     P->max_s = S.max_s;
+    P->cls.resize(S.nlevels);
+    for (int l = 0; l < S.nlevels; ++l) {
+        int nbig = 0, nmid = 0;
+        for (int q = S.levelptr[l]; q < S.levelptr[l + 1]; ++q) {
+            int sz = S.f_s[S.levelfronts[q]];
+            if (sz > FRONT_BIG) ++nbig;
+            else if (sz > FRONT_MID) ++nmid;
+        }
+        P->cls[l] = {nbig, nmid};
+    }
     P->d_fr = upload(fr);
     P->d_rowidx_orig = upload(S.rowidx_orig);
     P->d_children = upload(S.children);
@@ -537,10 +570,15 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
     size_t smem = (size_t)S.max_s * sizeof(cd);
     if (smem > 200 * 1024) throw InvalidArg("add_mat: largest front exceeds the solve kernels' shared memory");
     if (smem > 40 * 1024) {
-        CK(cudaFuncSetAttribute(fwd_level_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CK(cudaFuncSetAttribute(fwd_level_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CK(cudaFuncSetAttribute(bwd_level_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CK(cudaFuncSetAttribute(bwd_level_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        auto set = [&](auto kernel) {
+            CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        };
+        set(fwd_level_kernel<false, NT_BIG>); set(fwd_level_kernel<true, NT_BIG>);
+        set(bwd_level_kernel<false, NT_BIG>); set(bwd_level_kernel<true, NT_BIG>);
+        set(fwd_level_kernel<false, NT_MID>); set(fwd_level_kernel<true, NT_MID>);
+        set(bwd_level_kernel<false, NT_MID>); set(bwd_level_kernel<true, NT_MID>);
+        set(fwd_level_kernel<false, NT_SMALL>); set(fwd_level_kernel<true, NT_SMALL>);
+        set(bwd_level_kernel<false, NT_SMALL>); set(bwd_level_kernel<true, NT_SMALL>);
     }
     st->pats.push_back(std::move(P));
     if (solver_num) *solver_num = (int)st->pats.size() - 1;

@@ -184,84 +184,88 @@ constexpr int TW = 32;        // pivot tile width
 constexpr int TLD = TW + 1;   // shared-memory leading dimension
 
 struct TileSmem {
-    cd D[TW][TLD];
-    cd rowbuf[TW];
-    cd colbuf[TW];
+    cd D[2][TW][TLD];
     int piv[TW];
+    int src[TW];
     int sing;
 };
 
-// In-place Gauss-Jordan inversion of the n x n block in ts.D with partial pivoting
-// restricted to the block (row exchanges only move rows inside the pivot tile, so the
-// static front structure is unaffected: D^-1 absorbs the permutation).  All threads of
-// the CTA take part.  A zero / non-finite pivot sets ts.sing.
-__device__ __forceinline__ void invert_tile(TileSmem& ts, int n, int tid, int nthreads) {
-    const int lane = tid & 31, warp = tid >> 5;
+// Gauss-Jordan inversion of the n x n block in ts.D[0] with partial pivoting restricted to
+// the block (row exchanges only move rows inside the pivot tile, so the static front
+// structure is unaffected: D^-1 absorbs the permutation).  Double buffered: step p reads
+// D[cur] and writes D[cur^1], so one barrier per step suffices; every warp finds the pivot
+// row redundantly with shuffles.  Returns the buffer index holding D^-1.  A zero /
+// non-finite pivot sets ts.sing.  All NT threads of the CTA take part.
+template <int NT>
+__device__ __forceinline__ int invert_tile(TileSmem& ts, int n, int tid) {
+    const int lane = tid & 31;
+    int cur = 0;
     for (int p = 0; p < n; ++p) {
-        if (warp == 0) {
-            double m = -1.0;
-            if (lane >= p && lane < n) {
-                cd v = ts.D[lane][p];
-                m = fmax(fabs(v.x), fabs(v.y));
-                if (!(m == m)) m = -1.0;   // NaN never wins
-            }
-            int r = lane;
+        cd (*Dc)[TLD] = ts.D[cur];
+        cd (*Dn)[TLD] = ts.D[cur ^ 1];
+        double m = -1.0;
+        if (lane >= p && lane < n) {
+            cd v = Dc[lane][p];
+            m = fmax(fabs(v.x), fabs(v.y));
+            if (!(m == m)) m = -1.0;   // NaN never wins
+        }
+        int r = lane;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                double m2 = __shfl_xor_sync(0xffffffffu, m, o);
-                int r2 = __shfl_xor_sync(0xffffffffu, r, o);
-                if (m2 > m || (m2 == m && r2 < r)) { m = m2; r = r2; }
-            }
-            if (lane == 0) {
-                if (!(m > 0.0) || isinf(m)) { ts.sing = 1; r = p; }
-                ts.piv[p] = r;
-            }
+        for (int o = 16; o > 0; o >>= 1) {
+            double m2 = __shfl_xor_sync(0xffffffffu, m, o);
+            int r2 = __shfl_xor_sync(0xffffffffu, r, o);
+            if (m2 > m || (m2 == m && r2 < r)) { m = m2; r = r2; }
         }
-        __syncthreads();
-        const int r = ts.piv[p];
-        if (r != p && tid < n) {
-            cd tmp = ts.D[p][tid];
-            ts.D[p][tid] = ts.D[r][tid];
-            ts.D[r][tid] = tmp;
+        const bool ok = m > 0.0 && !isinf(m);
+        if (!ok) r = p;
+        if (tid == 0) {
+            ts.piv[p] = r;
+            if (!ok) ts.sing = 1;
         }
-        __syncthreads();
-        if (tid < n) {
-            cd piv = ts.D[p][p];
-            double m = fmax(fabs(piv.x), fabs(piv.y));
-            cd d = (m > 0.0 && !isinf(m) && m == m) ? crcp(piv) : make_double2(1.0, 0.0);
-            ts.rowbuf[tid] = (tid == p) ? d : cmul(ts.D[p][tid], d);
-        } else if (tid >= 32 && tid < 32 + n) {
-            ts.colbuf[tid - 32] = ts.D[tid - 32][p];
-        }
-        __syncthreads();
-        for (int e = tid; e < TW * TW; e += nthreads) {
-            int i = e >> 5, j = e & 31;
+        const cd d = ok ? crcp(Dc[r][p]) : make_double2(1.0, 0.0);
+        for (int e = tid; e < TW * TW; e += NT) {
+            const int i = e >> 5, j = e & 31;
             if (i >= n || j >= n) continue;
+            const cd rb = (j == p) ? d : cmul(Dc[r][j], d);
+            cd out;
             if (i == p) {
-                ts.D[i][j] = ts.rowbuf[j];
+                out = rb;
             } else {
-                cd base = (j == p) ? make_double2(0.0, 0.0) : ts.D[i][j];
-                cd f = ts.colbuf[i], rb = ts.rowbuf[j];
-                base.x = fma(-f.x, rb.x, base.x); base.x = fma(f.y, rb.y, base.x);
-                base.y = fma(-f.x, rb.y, base.y); base.y = fma(-f.y, rb.x, base.y);
-                ts.D[i][j] = base;
+                const int oi = (i == r) ? p : i;     // rows p and r trade places
+                const cd f = Dc[oi][p];
+                out = (j == p) ? make_double2(0.0, 0.0) : Dc[oi][j];
+                out.x = fma(-f.x, rb.x, out.x); out.x = fma(f.y, rb.y, out.x);
+                out.y = fma(-f.x, rb.y, out.y); out.y = fma(-f.y, rb.x, out.y);
             }
+            Dn[i][j] = out;
         }
         __syncthreads();
+        cur ^= 1;
     }
-    for (int p = n - 1; p >= 0; --p) {
-        const int r = ts.piv[p];
-        if (r != p && tid < n) {
-            cd tmp = ts.D[tid][p];
-            ts.D[tid][p] = ts.D[tid][r];
-            ts.D[tid][r] = tmp;
+    // undo the row exchanges: A^-1 = B P  <=>  column j of the result is column src[j] of B
+    if (tid == 0) {
+        bool any = false;
+        for (int j = 0; j < n; ++j) { ts.src[j] = j; any |= ts.piv[j] != j; }
+        for (int p = n - 1; p >= 0; --p) {
+            int r = ts.piv[p], t = ts.src[p];
+            ts.src[p] = ts.src[r];
+            ts.src[r] = t;
+        }
+        ts.piv[0] = any ? -1 : 0;     // flag: permutation is not the identity
+    }
+    __syncthreads();
+    if (ts.piv[0] < 0) {
+        for (int e = tid; e < TW * TW; e += NT) {
+            const int i = e >> 5, j = e & 31;
+            if (i < n && j < n) ts.D[cur ^ 1][i][j] = ts.D[cur][i][ts.src[j]];
         }
         __syncthreads();
+        cur ^= 1;
     }
+    return cur;
 }
 
 // ------------------------------------------------------------------- numeric factorisation
-constexpr int FACTOR_THREADS = 256;
 constexpr int KMAX = 32;   // component matrices supported by the fused assembly
 
 // One CTA per (front of this level, system): assemble the front (A entries + children's
@@ -269,15 +273,16 @@ constexpr int KMAX = 32;   // component matrices supported by the fused assembly
 //   FUSED = true : A entries are sum_k coef[b,k] * mats_f[k, q]  (mats_f in front-entry order),
 //                  also stored to vals[b, q] for the residual kernels
 //   FUSED = false: A entries are data[b, ent_src[q]]
-template <bool FUSED>
-__global__ void __launch_bounds__(FACTOR_THREADS, 2)
+template <bool FUSED, int NT>
+__global__ void __launch_bounds__(NT, 512 / NT)
 factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd* Fall,
                     const cd* __restrict__ data, const cd* __restrict__ coef,
                     const double* __restrict__ mats_f, int K, cd* vals, int* status) {
     __shared__ TileSmem ts;
     __shared__ cd coef_s[KMAX];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr int NW = FACTOR_THREADS / 32;
+    constexpr int NW = NT / 32;
+    constexpr int FACTOR_THREADS = NT;
     const int b = blockIdx.x % nsys;
     const FrontDesc fd = sd.fr[level_fronts[blockIdx.x / nsys]];
     cd* Fsys = Fall + (int64_t)b * sd.front_slots;
@@ -361,14 +366,14 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
         }
         for (int e = tid; e < TW * TW; e += FACTOR_THREADS) {
             int i = e >> 5, j = e & 31;
-            ts.D[i][j] = (i < jw && j < jw) ? F[(int64_t)(j0 + i) * ld + j0 + j]
-                                            : make_double2(i == j ? 1.0 : 0.0, 0.0);
+            if (i < jw && j < jw) ts.D[0][i][j] = F[(int64_t)(j0 + i) * ld + j0 + j];
         }
         __syncthreads();
-        invert_tile(ts, jw, tid, FACTOR_THREADS);
+        const int cur = invert_tile<NT>(ts, jw, tid);
+        const cd (*Dinv)[TLD] = ts.D[cur];
         for (int e = tid; e < TW * TW; e += FACTOR_THREADS) {
             int i = e >> 5, j = e & 31;
-            if (i < jw && j < jw) F[(int64_t)(j0 + i) * ld + j0 + j] = ts.D[i][j];
+            if (i < jw && j < jw) F[(int64_t)(j0 + i) * ld + j0 + j] = Dinv[i][j];
         }
         // Lt strip: rows [j1,s) x cols [j0,j1)  <-  F[rows, j0:j1] * D^-1
         const int nlt = (s - j1 + 15) >> 4;
@@ -376,7 +381,7 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
             int r = j1 + 16 * tile, mr = min(16, s - r);
             Acc<2, 4> acc;
             acc.zero();
-            warp_gemm<2, 4>(acc, F + (int64_t)r * ld + j0, ld, mr, &ts.D[0][0], TLD, jw, jw, lane);
+            warp_gemm<2, 4>(acc, F + (int64_t)r * ld + j0, ld, mr, &Dinv[0][0], TLD, jw, jw, lane);
             store_tile<2, 4, false>(acc, F + (int64_t)r * ld + j0, ld, mr, jw, lane);
         }
         __syncthreads();
@@ -398,7 +403,6 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
 }
 
 // ------------------------------------------------------------------------ triangular solves
-constexpr int SOLVE_THREADS = 256;
 
 // rhs / solution addressing: system b, right-hand side j
 struct VecView {
@@ -411,13 +415,14 @@ struct VecView {
 
 // Forward sweep over one level.  TRANS = false: Lt (unit block lower);  TRANS = true:
 // Ubar^T (block lower with D_J^T on the diagonal) -- the first half of A^T x = b.
-template <bool TRANS>
-__global__ void __launch_bounds__(SOLVE_THREADS)
+template <bool TRANS, int NT>
+__global__ void __launch_bounds__(NT)
 fwd_level_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __restrict__ Fall,
                  VecView vv) {
     extern __shared__ cd v[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr int NW = SOLVE_THREADS / 32;
+    constexpr int SOLVE_THREADS = NT;
+    constexpr int NW = NT / 32;
     int bid = blockIdx.x;
     const int b = bid % vv.nsys;
     bid /= vv.nsys;
@@ -483,15 +488,16 @@ fwd_level_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __re
 }
 
 // Backward sweep over one level.  TRANS = false: Ubar ; TRANS = true: Lt^T.
-template <bool TRANS>
-__global__ void __launch_bounds__(SOLVE_THREADS)
+template <bool TRANS, int NT>
+__global__ void __launch_bounds__(NT)
 bwd_level_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __restrict__ Fall,
                  VecView vv) {
     extern __shared__ cd v[];
-    __shared__ cd part[SOLVE_THREADS / 32][TW];
+    constexpr int SOLVE_THREADS = NT;
+    constexpr int NW = NT / 32;
+    __shared__ cd part[NW][TW];
     __shared__ cd tbuf[TW];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr int NW = SOLVE_THREADS / 32;
     int bid = blockIdx.x;
     const int b = bid % vv.nsys;
     bid /= vv.nsys;
@@ -709,47 +715,73 @@ __global__ void scale_rhs_kernel(int N, const double* __restrict__ rhs_vec,
 }
 
 // K5: partial[chunk, b, k] = - sum_{e in chunk} mats[k, e] * lam[b, row e] * u[b, col e]
+// This is the GEMM  C[B x K] = W[B x nnz] * M^T[nnz x K]  with W never materialised
+// (w_be = lam_b[row e] * u_b[col e] is formed in registers as the A fragment), run on the
+// FP64 tensor cores: per warp 8 systems x 4 entries x 32 components per DMMA group.
+// A block stages GRAD_E entries of all K matrices (+ their row/col indices) in shared
+// memory and serves 8 warps x 8 systems with them; GRAD_SUB such slices per block.
 constexpr int GRAD_THREADS = 256;
-constexpr int GRAD_PER_THREAD = 4;
-template <int KK>
+constexpr int GRAD_E = 256;
+constexpr int GRAD_SUB = 8;
+constexpr int GRAD_CHUNK = GRAD_E * GRAD_SUB;      // entries per block
+constexpr int GRAD_SYS = 8 * (GRAD_THREADS / 32);  // systems per block
+constexpr int GRAD_LD = GRAD_E + 4;
+constexpr size_t GRAD_SMEM = (size_t)KMAX * GRAD_LD * sizeof(double) + 2 * GRAD_E * sizeof(int);
+
 __global__ void __launch_bounds__(GRAD_THREADS)
 grad_kernel(int64_t nnz, int N, int K, const int* __restrict__ row, const int* __restrict__ col,
             const double* __restrict__ mats, const cd* __restrict__ lam, const cd* __restrict__ u,
-            cd* partial, int nsys) {
-    __shared__ cd red[GRAD_THREADS / 32][KK];
-    const int b = blockIdx.x % nsys, chunk = blockIdx.x / nsys;
+            cd* partial, int nsys, int ngroups) {
+    extern __shared__ double gsm[];
+    double (*ms)[GRAD_LD] = reinterpret_cast<double (*)[GRAD_LD]>(gsm);
+    int* rs = reinterpret_cast<int*>(gsm + (size_t)KMAX * GRAD_LD);
+    int* cs = rs + GRAD_E;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const cd* lb = lam + (int64_t)b * N;
-    const cd* ub = u + (int64_t)b * N;
-    cd acc[KK];
+    const int g = lane >> 2, t = lane & 3;
+    const int group = blockIdx.x % ngroups, chunk = blockIdx.x / ngroups;
+    const int b = group * GRAD_SYS + warp * 8 + g;
+    const bool valid = b < nsys;
+    const cd* lb = lam + (int64_t)(valid ? b : 0) * N;
+    const cd* ub = u + (int64_t)(valid ? b : 0) * N;
+    double re[KMAX / 8][2], im[KMAX / 8][2];
 #pragma unroll
-    for (int kk = 0; kk < KK; ++kk) acc[kk] = make_double2(0.0, 0.0);
-    const int64_t e0 = (int64_t)chunk * GRAD_THREADS * GRAD_PER_THREAD;
+    for (int nb = 0; nb < KMAX / 8; ++nb) { re[nb][0] = re[nb][1] = im[nb][0] = im[nb][1] = 0.0; }
+    for (int sub = 0; sub < GRAD_SUB; ++sub) {
+        const int64_t e0 = (int64_t)chunk * GRAD_CHUNK + (int64_t)sub * GRAD_E;
+        if (e0 >= nnz) break;
+        __syncthreads();
+        for (int idx = tid; idx < KMAX * GRAD_E; idx += GRAD_THREADS) {
+            const int kk = idx / GRAD_E, e = idx % GRAD_E;
+            ms[kk][e] = (kk < K && e0 + e < nnz) ? mats[(int64_t)kk * nnz + e0 + e] : 0.0;
+        }
+        for (int e = tid; e < GRAD_E; e += GRAD_THREADS) {
+            const bool in = e0 + e < nnz;
+            rs[e] = in ? row[e0 + e] : 0;
+            cs[e] = in ? col[e0 + e] : 0;
+        }
+        __syncthreads();
+#pragma unroll 2
+        for (int e4 = 0; e4 < GRAD_E; e4 += 4) {
+            const int e = e4 + t;
+            cd w = cmul(lb[rs[e]], ub[cs[e]]);
+            if (!valid) w = make_double2(0.0, 0.0);
 #pragma unroll
-    for (int it = 0; it < GRAD_PER_THREAD; ++it) {
-        int64_t e = e0 + it * GRAD_THREADS + tid;
-        if (e < nnz) {
-            cd w = cmul(lb[row[e]], ub[col[e]]);
-#pragma unroll
-            for (int kk = 0; kk < KK; ++kk)
-                if (kk < K) {
-                    double m = mats[(int64_t)kk * nnz + e];
-                    acc[kk].x = fma(-m, w.x, acc[kk].x);
-                    acc[kk].y = fma(-m, w.y, acc[kk].y);
-                }
+            for (int nb = 0; nb < KMAX / 8; ++nb) {
+                const double m = ms[8 * nb + g][e];
+                dmma(re[nb][0], re[nb][1], w.x, m);
+                dmma(im[nb][0], im[nb][1], w.y, m);
+            }
         }
     }
+    if (valid) {
+        cd* out = partial + ((int64_t)chunk * nsys + b) * K;
 #pragma unroll
-    for (int kk = 0; kk < KK; ++kk) {
-        cd v = warp_sum(acc[kk]);
-        if (lane == 0) red[warp][kk] = v;
-    }
-    __syncthreads();
-    if (tid < K) {
-        cd v = make_double2(0.0, 0.0);
+        for (int nb = 0; nb < KMAX / 8; ++nb)
 #pragma unroll
-        for (int w = 0; w < GRAD_THREADS / 32; ++w) { v.x += red[w][tid].x; v.y += red[w][tid].y; }
-        partial[((int64_t)chunk * nsys + b) * K + tid] = v;
+            for (int e = 0; e < 2; ++e) {
+                const int kk = 8 * nb + 2 * t + e;
+                if (kk < K) out[kk] = make_double2(-re[nb][e], -im[nb][e]);
+            }
     }
 }
 
