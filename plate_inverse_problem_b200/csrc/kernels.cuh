@@ -223,9 +223,9 @@ __device__ __forceinline__ int invert_tile(TileSmem& ts, int n, int tid) {
             if (!ok) ts.sing = 1;
         }
         const cd d = ok ? crcp(Dc[r][p]) : make_double2(1.0, 0.0);
-        for (int e = tid; e < TW * TW; e += NT) {
+        for (int e = tid; e < n * TW; e += NT) {
             const int i = e >> 5, j = e & 31;
-            if (i >= n || j >= n) continue;
+            if (j >= n) continue;
             const cd rb = (j == p) ? d : cmul(Dc[r][j], d);
             cd out;
             if (i == p) {
@@ -255,9 +255,9 @@ __device__ __forceinline__ int invert_tile(TileSmem& ts, int n, int tid) {
     }
     __syncthreads();
     if (ts.piv[0] < 0) {
-        for (int e = tid; e < TW * TW; e += NT) {
+        for (int e = tid; e < n * TW; e += NT) {
             const int i = e >> 5, j = e & 31;
-            if (i < n && j < n) ts.D[cur ^ 1][i][j] = ts.D[cur][i][ts.src[j]];
+            if (j < n) ts.D[cur ^ 1][i][j] = ts.D[cur][i][ts.src[j]];
         }
         __syncthreads();
         cur ^= 1;
@@ -321,17 +321,31 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
         const int* rel = sd.relmap + fc.reloff;
         const int mc = fc.s - fc.k;
         const cd* Fc = Fsys + fc.off + (int64_t)fc.k * fc.ld + fc.k;
-        for (int i = warp; i < mc; i += NW) {
-            cd* prow = F + (int64_t)rel[i] * ld;
-            const cd* crow = Fc + (int64_t)i * fc.ld;
-            for (int j = lane; j < mc; j += 32) {
-                cd v = crow[j];
-                cd* p = prow + rel[j];
-                cd o = *p;
-                o.x += v.x;
-                o.y += v.y;
-                *p = o;
+        // flattened (i, j) over all threads, four independent elements in flight per
+        // thread: the child's block streams from HBM, the parent's slots sit in L2, and a
+        // dependent load->add->store chain per element would leave both idle.
+        const int tot = mc * mc;
+        for (int e0 = tid; e0 < tot; e0 += 4 * FACTOR_THREADS) {
+            cd v[4];
+            cd* p[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int e = e0 + q * FACTOR_THREADS;
+                if (e < tot) {
+                    const int i = e / mc, j = e - i * mc;
+                    v[q] = Fc[(int64_t)i * fc.ld + j];
+                    p[q] = F + (int64_t)rel[i] * ld + rel[j];
+                } else {
+                    p[q] = nullptr;
+                }
             }
+            cd o[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (p[q]) o[q] = *p[q];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (p[q]) *p[q] = make_double2(o[q].x + v[q].x, o[q].y + v[q].y);
         }
         __syncthreads();
     }
@@ -364,16 +378,16 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
             }
             __syncthreads();
         }
-        for (int e = tid; e < TW * TW; e += FACTOR_THREADS) {
+        for (int e = tid; e < jw * TW; e += FACTOR_THREADS) {
             int i = e >> 5, j = e & 31;
-            if (i < jw && j < jw) ts.D[0][i][j] = F[(int64_t)(j0 + i) * ld + j0 + j];
+            if (j < jw) ts.D[0][i][j] = F[(int64_t)(j0 + i) * ld + j0 + j];
         }
         __syncthreads();
         const int cur = invert_tile<NT>(ts, jw, tid);
         const cd (*Dinv)[TLD] = ts.D[cur];
-        for (int e = tid; e < TW * TW; e += FACTOR_THREADS) {
+        for (int e = tid; e < jw * TW; e += FACTOR_THREADS) {
             int i = e >> 5, j = e & 31;
-            if (i < jw && j < jw) F[(int64_t)(j0 + i) * ld + j0 + j] = Dinv[i][j];
+            if (j < jw) F[(int64_t)(j0 + i) * ld + j0 + j] = Dinv[i][j];
         }
         // Lt strip: rows [j1,s) x cols [j0,j1)  <-  F[rows, j0:j1] * D^-1
         const int nlt = (s - j1 + 15) >> 4;
@@ -456,19 +470,29 @@ fwd_level_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __re
         if (!TRANS) {
             // v[i] -= Lt[i, J] . v_J  for rows below the tile: warp per row, lane per column
             const cd vj = lane < jw ? v[j0 + lane] : make_double2(0.0, 0.0);
-            for (int i = j1 + warp; i < s; i += NW) {
-                cd acc = make_double2(0.0, 0.0);
-                if (lane < jw) acc = cmul(F[(int64_t)i * ld + j0 + lane], vj);
-                acc = warp_sum(acc);
-                if (lane == 0) { v[i].x -= acc.x; v[i].y -= acc.y; }
+            for (int i = j1 + 4 * warp; i < s; i += 4 * NW) {
+                cd a[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    a[q] = (lane < jw && i + q < s) ? F[(int64_t)(i + q) * ld + j0 + lane]
+                                                     : make_double2(0.0, 0.0);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) a[q] = warp_sum(cmul(a[q], vj));
+                if (lane == 0) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if (i + q < s) { v[i + q].x -= a[q].x; v[i + q].y -= a[q].y; }
+                }
             }
             __syncthreads();
         } else {
             // z_J = D_J^-T v_J
             if (warp == 0) {
                 cd z = make_double2(0.0, 0.0);
-                if (lane < jw)
+                if (lane < jw) {
+#pragma unroll 8
                     for (int p = 0; p < jw; ++p) cfma(z, F[(int64_t)(j0 + p) * ld + j0 + lane], v[j0 + p]);
+                }
                 __syncwarp();
                 if (lane < jw) v[j0 + lane] = z;
             }
@@ -476,6 +500,7 @@ fwd_level_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __re
             // v[j] -= sum_p U[J_p, j] z_p  for columns right of the tile: thread per column
             for (int j = j1 + tid; j < s; j += SOLVE_THREADS) {
                 cd acc = make_double2(0.0, 0.0);
+#pragma unroll 8
                 for (int p = 0; p < jw; ++p) cfma(acc, F[(int64_t)(j0 + p) * ld + j], v[j0 + p]);
                 v[j].x -= acc.x;
                 v[j].y -= acc.y;
@@ -519,6 +544,7 @@ bwd_level_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __re
             for (int p = warp; p < jw; p += NW) {
                 const cd* row = F + (int64_t)(j0 + p) * ld;
                 cd acc = make_double2(0.0, 0.0);
+#pragma unroll 4
                 for (int j = j1 + lane; j < s; j += 32) cfma(acc, row[j], v[j]);
                 acc = warp_sum(acc);
                 if (lane == 0) tbuf[p] = make_double2(v[j0 + p].x - acc.x, v[j0 + p].y - acc.y);
@@ -535,8 +561,10 @@ bwd_level_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __re
         } else {
             // v[j0+q] -= sum_{i >= j1} Lt[i, j0+q] v[i] : lane per column, warps stride the rows
             cd acc = make_double2(0.0, 0.0);
-            if (lane < jw)
+            if (lane < jw) {
+#pragma unroll 4
                 for (int i = j1 + warp; i < s; i += NW) cfma(acc, F[(int64_t)i * ld + j0 + lane], v[i]);
+            }
             part[warp][lane] = acc;
             __syncthreads();
             if (tid < jw) {
