@@ -235,20 +235,26 @@ void for_each_class(jpb_state* st, Pattern& P, int l, int64_t mult, Launch&& lau
     }
 }
 
-// numeric factorisation of `nsys` systems into F
-void factor(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* F, const cd* data, const cd* coef,
-            cd* vals, int* status) {
+// K1: vals[b, q] = sum_k coef[b, k] * mats_f[k, q]  (front-entry order), mats read once per
+// slice of ASM_BCHUNK systems
+constexpr int ASM_BCHUNK = 32;
+void assemble_entries(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, const cd* coef, cd* vals) {
+    dim3 grid((unsigned)((P.S.nnz + 255) / 256), (unsigned)((nsys + ASM_BCHUNK - 1) / ASM_BCHUNK));
+    assemble_kernel<KMAX><<<grid, 256, (size_t)ASM_BCHUNK * P.K * 16, s>>>(P.S.nnz, P.K, nsys, P.d_mats_f, coef,
+                                                                         vals, ASM_BCHUNK);
+    launch_check(st);
+}
+
+// numeric factorisation of `nsys` systems into F.  ent_order: `data` is [nsys, nnz] in
+// front-entry order (from assemble_entries) instead of the caller's CSC order.
+void factor(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* F, const cd* data, bool ent_order,
+            int* status) {
     Span span(st, s, PH_FACTOR);
-    const bool fused = data == nullptr;
     for (int l = 0; l < P.S.nlevels; ++l) {
         for_each_class(st, P, l, nsys, [&](int c, const int* lf, unsigned grid) {
-#define JPB_FACTOR(NT)                                                                              \
-    if (fused)                                                                                      \
-        factor_level_kernel<true, NT><<<grid, NT, 0, s>>>(P.sd, lf, nsys, F, nullptr, coef, P.d_mats_f, \
-                                                          P.K, vals, status);                       \
-    else                                                                                            \
-        factor_level_kernel<false, NT><<<grid, NT, 0, s>>>(P.sd, lf, nsys, F, data, nullptr, nullptr, 0, \
-                                                           nullptr, status);
+#define JPB_FACTOR(NT)                                                                          \
+    if (ent_order) factor_level_kernel<true, NT><<<grid, NT, 0, s>>>(P.sd, lf, nsys, F, data, status); \
+    else factor_level_kernel<false, NT><<<grid, NT, 0, s>>>(P.sd, lf, nsys, F, data, status);
             if (c == 0) { JPB_FACTOR(NT_BIG) } else if (c == 1) { JPB_FACTOR(NT_MID) } else { JPB_FACTOR(NT_SMALL) }
 #undef JPB_FACTOR
         });
@@ -370,7 +376,11 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
 
     for (int64_t b0 = 0; b0 < B; b0 += W) {
         const int nw = (int)std::min<int64_t>(W, B - b0);
-        factor(st, s, P, nw, F, nullptr, coef + b0 * K, vals, status ? status + b0 : nullptr);
+        {
+            Span span(st, s, PH_FACTOR);
+            assemble_entries(st, s, P, nw, coef + b0 * K, vals);
+        }
+        factor(st, s, P, nw, F, vals, true, status ? status + b0 : nullptr);
         {
             dim3 grid((N + 255) / 256, nw);
             scale_rhs_kernel<<<grid, 256, 0, s>>>(N, P.d_rhs_vec, scale + b0, vb);
@@ -644,7 +654,7 @@ int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const doub
             Span span(st, s, PH_H2D);
             CK(cudaMemcpyAsync(dat, (const cd*)data + i0 * nnz, (size_t)nw * nnz * 16, cudaMemcpyHostToDevice, s));
         }
-        factor(st, s, P, nw, F, dat, nullptr, nullptr, dstat + i0);
+        factor(st, s, P, nw, F, dat, false, dstat + i0);
         for (int64_t j0 = 0; j0 < ms.nrhs; j0 += JC) {
             const int nj = (int)std::min<int64_t>(JC, ms.nrhs - j0);
             // stage rhs(b, j) densely as vb[(j * nw + b) * N]

@@ -203,26 +203,33 @@ __device__ __forceinline__ int invert_tile(TileSmem& ts, int n, int tid) {
     for (int p = 0; p < n; ++p) {
         cd (*Dc)[TLD] = ts.D[cur];
         cd (*Dn)[TLD] = ts.D[cur ^ 1];
-        double m = -1.0;
+        // pivot row = argmax over rows >= p of max(|re|, |im|), compared on the upper 27 bits
+        // of the double (sign-free exponent + 16 mantissa bits: ample for a pivot choice)
+        // so that one integer warp reduction does the search; ties go to the lowest row.
+        unsigned key = 0u;
         if (lane >= p && lane < n) {
-            cd v = Dc[lane][p];
-            m = fmax(fabs(v.x), fabs(v.y));
-            if (!(m == m)) m = -1.0;   // NaN never wins
+            const cd v = Dc[lane][p];
+            const double m = fmax(fabs(v.x), fabs(v.y));
+            const unsigned hi = (unsigned)__double2hiint(m);
+            if (m == m && hi < 0x7ff00000u) key = ((hi >> 4) << 5) | (unsigned)(31 - lane);
         }
-        int r = lane;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            double m2 = __shfl_xor_sync(0xffffffffu, m, o);
-            int r2 = __shfl_xor_sync(0xffffffffu, r, o);
-            if (m2 > m || (m2 == m && r2 < r)) { m = m2; r = r2; }
-        }
-        const bool ok = m > 0.0 && !isinf(m);
-        if (!ok) r = p;
+        key = __reduce_max_sync(0xffffffffu, key);
+        const bool ok = (key >> 5) != 0u;
+        const int r = ok ? 31 - (int)(key & 31u) : p;
         if (tid == 0) {
             ts.piv[p] = r;
             if (!ok) ts.sing = 1;
         }
-        const cd d = ok ? crcp(Dc[r][p]) : make_double2(1.0, 0.0);
+        cd d = make_double2(1.0, 0.0);
+        if (ok) {
+            // 1/z = conj(z) / |z|^2 after scaling z by 2^-e to dodge over/underflow: one division
+            const cd z = Dc[r][p];
+            const int ex = ((int)(key >> 21)) - 1023;          // exponent of max(|re|, |im|)
+            const double sc = __hiloint2double((1023 - ex) << 20, 0);   // 2^-ex, exact
+            const double zx = z.x * sc, zy = z.y * sc;
+            const double q = sc / fma(zx, zx, zy * zy);
+            d = make_double2(zx * q, -zy * q);
+        }
         for (int e = tid; e < n * TW; e += NT) {
             const int i = e >> 5, j = e & 31;
             if (j >= n) continue;
@@ -273,13 +280,11 @@ constexpr int KMAX = 32;   // component matrices supported by the fused assembly
 //   FUSED = true : A entries are sum_k coef[b,k] * mats_f[k, q]  (mats_f in front-entry order),
 //                  also stored to vals[b, q] for the residual kernels
 //   FUSED = false: A entries are data[b, ent_src[q]]
-template <bool FUSED, int NT>
+template <bool ENT_ORDER, int NT>
 __global__ void __launch_bounds__(NT, 512 / NT)
 factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd* Fall,
-                    const cd* __restrict__ data, const cd* __restrict__ coef,
-                    const double* __restrict__ mats_f, int K, cd* vals, int* status) {
+                    const cd* __restrict__ data, int* status) {
     __shared__ TileSmem ts;
-    __shared__ cd coef_s[KMAX];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = NT / 32;
     constexpr int FACTOR_THREADS = NT;
@@ -290,7 +295,6 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
     const int s = fd.s, k = fd.k, ld = fd.ld;
 
     if (tid == 0) ts.sing = 0;
-    if (FUSED && tid < K) coef_s[tid] = coef[(int64_t)b * K + tid];
     // ---- zero, then A entries (every entry owns its slot), then the children one by one
     {
         const cd zero = make_double2(0.0, 0.0);
@@ -298,22 +302,14 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
         for (int e = tid; e < tot; e += FACTOR_THREADS) F[e] = zero;
     }
     __syncthreads();
-    for (int q = tid; q < fd.nent; q += FACTOR_THREADS) {
-        const int64_t gq = fd.entptr + q;
-        cd v;
-        if (FUSED) {
-            v = make_double2(0.0, 0.0);
-            for (int kk = 0; kk < K; ++kk) {
-                double m = mats_f[(int64_t)kk * sd.nnz + gq];
-                cd c = coef_s[kk];
-                v.x = fma(c.x, m, v.x);
-                v.y = fma(c.y, m, v.y);
-            }
-            vals[(int64_t)b * sd.nnz + gq] = v;
-        } else {
-            v = data[(int64_t)b * sd.nnz + sd.ent_src[gq]];
+    // A entries: ENT_ORDER = true : data[b, q] already in front-entry order (written by the
+    // assembly kernel K1, coalesced here); false: data[b, ent_src[q]] in the caller's CSC order
+    {
+        const cd* db = data + (int64_t)b * sd.nnz;
+        for (int q = tid; q < fd.nent; q += FACTOR_THREADS) {
+            const int64_t gq = fd.entptr + q;
+            F[sd.ent_slot[gq]] = ENT_ORDER ? db[gq] : db[sd.ent_src[gq]];
         }
-        F[sd.ent_slot[gq]] = v;
     }
     __syncthreads();
     for (int ci = 0; ci < fd.nchild; ++ci) {
@@ -321,15 +317,16 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
         const int* rel = sd.relmap + fc.reloff;
         const int mc = fc.s - fc.k;
         const cd* Fc = Fsys + fc.off + (int64_t)fc.k * fc.ld + fc.k;
-        // flattened (i, j) over all threads, four independent elements in flight per
+        // flattened (i, j) over all threads, eight independent elements in flight per
         // thread: the child's block streams from HBM, the parent's slots sit in L2, and a
         // dependent load->add->store chain per element would leave both idle.
         const int tot = mc * mc;
-        for (int e0 = tid; e0 < tot; e0 += 4 * FACTOR_THREADS) {
-            cd v[4];
-            cd* p[4];
+        constexpr int MLP = 8;
+        for (int e0 = tid; e0 < tot; e0 += MLP * FACTOR_THREADS) {
+            cd v[MLP];
+            cd* p[MLP];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
+            for (int q = 0; q < MLP; ++q) {
                 const int e = e0 + q * FACTOR_THREADS;
                 if (e < tot) {
                     const int i = e / mc, j = e - i * mc;
@@ -339,12 +336,12 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
                     p[q] = nullptr;
                 }
             }
-            cd o[4];
+            cd o[MLP];
 #pragma unroll
-            for (int q = 0; q < 4; ++q)
+            for (int q = 0; q < MLP; ++q)
                 if (p[q]) o[q] = *p[q];
 #pragma unroll
-            for (int q = 0; q < 4; ++q)
+            for (int q = 0; q < MLP; ++q)
                 if (p[q]) *p[q] = make_double2(o[q].x + v[q].x, o[q].y + v[q].y);
         }
         __syncthreads();
