@@ -8,6 +8,7 @@
 #include <array>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <stdexcept>
@@ -215,9 +216,31 @@ void launch_check(jpb_state* st) {
     if (e != cudaSuccess) throw CudaError(std::string("kernel launch failed: ") + cudaGetErrorString(e));
 }
 
-// size classes of fronts: CTA width follows the front order
-constexpr int FRONT_BIG = 128, FRONT_MID = 48;
-constexpr int NT_BIG = 256, NT_MID = 128, NT_SMALL = 64;
+// size classes of fronts: CTA width follows the front order.  Defaults can be overridden
+// for tuning runs with JPB_FRONT_BIG / JPB_FRONT_MID / JPB_NT_BIG / JPB_NT_MID / JPB_NT_SMALL.
+struct Tuning {
+    int front_big = 128, front_mid = 64;
+    int nt[3] = {256, 128, 64};
+    Tuning() {
+        auto geti = [](const char* name, int def) {
+            const char* v = getenv(name);
+            return v ? atoi(v) : def;
+        };
+        front_big = geti("JPB_FRONT_BIG", front_big);
+        front_mid = geti("JPB_FRONT_MID", front_mid);
+        nt[0] = geti("JPB_NT_BIG", nt[0]);
+        nt[1] = geti("JPB_NT_MID", nt[1]);
+        nt[2] = geti("JPB_NT_SMALL", nt[2]);
+        for (int& v : nt)
+            if (v != 64 && v != 128 && v != 256) v = 128;
+    }
+};
+const Tuning& tuning() {
+    static Tuning t;
+    return t;
+}
+#define FRONT_BIG (tuning().front_big)
+#define FRONT_MID (tuning().front_mid)
 
 template <class Launch>
 void for_each_class(jpb_state* st, Pattern& P, int l, int64_t mult, Launch&& launch) {
@@ -255,7 +278,8 @@ void factor(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* F, const cd
 #define JPB_FACTOR(NT)                                                                          \
     if (ent_order) factor_level_kernel<true, NT><<<grid, NT, 0, s>>>(P.sd, lf, nsys, F, data, status); \
     else factor_level_kernel<false, NT><<<grid, NT, 0, s>>>(P.sd, lf, nsys, F, data, status);
-            if (c == 0) { JPB_FACTOR(NT_BIG) } else if (c == 1) { JPB_FACTOR(NT_MID) } else { JPB_FACTOR(NT_SMALL) }
+            const int nt = tuning().nt[c];
+            if (nt == 256) { JPB_FACTOR(256) } else if (nt == 128) { JPB_FACTOR(128) } else { JPB_FACTOR(64) }
 #undef JPB_FACTOR
         });
     }
@@ -271,15 +295,17 @@ void tri_solve(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool tran
     else KERNEL<false, NT><<<grid, NT, smem, s>>>(P.sd, lf, F, vv);
     for (int l = 0; l < P.S.nlevels; ++l)
         for_each_class(st, P, l, mult, [&](int c, const int* lf, unsigned grid) {
-            if (c == 0) { JPB_SOLVE(fwd_level_kernel, NT_BIG) }
-            else if (c == 1) { JPB_SOLVE(fwd_level_kernel, NT_MID) }
-            else { JPB_SOLVE(fwd_level_kernel, NT_SMALL) }
+            const int nt = tuning().nt[c];
+            if (nt == 256) { JPB_SOLVE(fwd_level_kernel, 256) }
+            else if (nt == 128) { JPB_SOLVE(fwd_level_kernel, 128) }
+            else { JPB_SOLVE(fwd_level_kernel, 64) }
         });
     for (int l = P.S.nlevels - 1; l >= 0; --l)
         for_each_class(st, P, l, mult, [&](int c, const int* lf, unsigned grid) {
-            if (c == 0) { JPB_SOLVE(bwd_level_kernel, NT_BIG) }
-            else if (c == 1) { JPB_SOLVE(bwd_level_kernel, NT_MID) }
-            else { JPB_SOLVE(bwd_level_kernel, NT_SMALL) }
+            const int nt = tuning().nt[c];
+            if (nt == 256) { JPB_SOLVE(bwd_level_kernel, 256) }
+            else if (nt == 128) { JPB_SOLVE(bwd_level_kernel, 128) }
+            else { JPB_SOLVE(bwd_level_kernel, 64) }
         });
 #undef JPB_SOLVE
 }
@@ -583,12 +609,12 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
         auto set = [&](auto kernel) {
             CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         };
-        set(fwd_level_kernel<false, NT_BIG>); set(fwd_level_kernel<true, NT_BIG>);
-        set(bwd_level_kernel<false, NT_BIG>); set(bwd_level_kernel<true, NT_BIG>);
-        set(fwd_level_kernel<false, NT_MID>); set(fwd_level_kernel<true, NT_MID>);
-        set(bwd_level_kernel<false, NT_MID>); set(bwd_level_kernel<true, NT_MID>);
-        set(fwd_level_kernel<false, NT_SMALL>); set(fwd_level_kernel<true, NT_SMALL>);
-        set(bwd_level_kernel<false, NT_SMALL>); set(bwd_level_kernel<true, NT_SMALL>);
+        set(fwd_level_kernel<false, 256>); set(fwd_level_kernel<true, 256>);
+        set(bwd_level_kernel<false, 256>); set(bwd_level_kernel<true, 256>);
+        set(fwd_level_kernel<false, 128>); set(fwd_level_kernel<true, 128>);
+        set(bwd_level_kernel<false, 128>); set(bwd_level_kernel<true, 128>);
+        set(fwd_level_kernel<false, 64>); set(fwd_level_kernel<true, 64>);
+        set(bwd_level_kernel<false, 64>); set(bwd_level_kernel<true, 64>);
     }
     st->pats.push_back(std::move(P));
     if (solver_num) *solver_num = (int)st->pats.size() - 1;
