@@ -21,7 +21,7 @@ from typing import Callable
 
 import numpy as np
 
-from . import _lib
+from . import _lib, parallel
 from .Material import Material, coefficients_and_jacobian
 from .Sparse import find_permutation, symbolic_indices
 
@@ -146,19 +146,6 @@ class Problem:
     def symbolic_info(self):
         return self._st.symbolic_info(self.solver_num)
 
-    @staticmethod
-    def _shard(n):
-        """Contiguous block of [0, n) owned by this rank."""
-        try:
-            import torch.distributed as dist
-            if dist.is_available() and dist.is_initialized():
-                r, w = dist.get_rank(), dist.get_world_size()
-                lo, hi = (n * r) // w, (n * (r + 1)) // w
-                return lo, hi, dist
-        except ImportError:
-            pass
-        return 0, n, None
-
     # ---- forward -------------------------------------------------------------------------
     def _forward_raw(self, freqs, params, return_u=False):
         freqs = np.atleast_1d(np.asarray(freqs, dtype=np.float64))
@@ -177,17 +164,8 @@ class Problem:
         """`Problem.py:377-518`: f(freqs[F], params[P]) -> fr[F] (real amplitudes)."""
         def fr_function(freqs, params):
             freqs = np.atleast_1d(np.asarray(freqs, dtype=np.float64))
-            lo, hi, dist = self._shard(freqs.size)
-            fr = np.zeros(freqs.size)
-            if hi > lo:
-                fr[lo:hi] = self._forward_raw(freqs[lo:hi], params)[0]
-            if dist is not None:
-                import torch
-                dev = torch.device("cuda", self._st.device) if dist.get_backend() == "nccl" else "cpu"
-                t = torch.from_numpy(fr).to(dev)
-                dist.all_reduce(t)
-                fr = t.cpu().numpy()
-            return fr
+            return parallel.sharded_gather(lambda lo, hi: self._forward_raw(freqs[lo:hi], params)[0],
+                                           freqs.size, self._st.device)
         return fr_function
 
     def solveForward(self, freqs, params=None):
@@ -211,10 +189,9 @@ class Problem:
 
         def value_and_grad(params):
             p = np.asarray(params, dtype=np.float64) * scaling
-            lo, hi, dist = self._shard(F)
-            nloc = hi - lo
-            acc = np.zeros(1 + p.size)
-            if nloc > 0:
+
+            def local(lo, hi):
+                nloc = hi - lo
                 coef, s, dc, ds = self.coefficients(frequencies[lo:hi], p, with_jacobian=True)
                 coef, s = np.ascontiguousarray(coef), np.ascontiguousarray(s)
                 ref = np.ascontiguousarray(reference_fr[lo:hi])
@@ -226,17 +203,13 @@ class Problem:
                                                    _lib.ptr(ref), _lib.ptr(self.weights), ltype, F,
                                                    _lib.ptr(fr), _lib.ptr(loss_sum), _lib.ptr(ct),
                                                    _lib.ptr(cts), None))
-                acc[0] = loss_sum[0] / F
-                # chain rule through the coefficient functions (SURVEY App. D)
-                acc[1:] = np.real(np.einsum("fk,fkp->p", ct, dc) + np.einsum("f,fp->p", cts, ds))
                 value_and_grad.last_fr = fr
-            if dist is not None:
-                import torch
-                dev = torch.device("cuda", self._st.device) if dist.get_backend() == "nccl" else "cpu"
-                t = torch.from_numpy(acc).to(dev)
-                dist.all_reduce(t)          # the single collective of the path
-                acc = t.cpu().numpy()
-            return float(acc[0]), acc[1:] * scaling
+                # chain rule through the coefficient functions (SURVEY App. D)
+                g = np.real(np.einsum("fk,fkp->p", ct, dc) + np.einsum("f,fp->p", cts, ds))
+                return loss_sum[0] / F, g
+
+            val, grad = parallel.sharded_value_and_grad(local, F, p.size, self._st.device)   # ONE all-reduce
+            return val, grad * scaling
 
         fr_function = self.getFRFunction()
 

@@ -281,3 +281,29 @@ def test_torch_autograd_binding(tiny):
     Am[r, c] -= h
     fd = (f(Ap, b.detach().numpy()) - f(Am, b.detach().numpy())) / (2 * h)
     assert abs(d.grad[e].real.item() - fd) <= 1e-5 * abs(fd) + 1e-12
+
+
+def test_two_shards_equal_one(small):
+    """F_total semantics of jpb_eval_loss_grad: two half-sweeps evaluated separately (as two
+    ranks would) sum to the single-call result -- the quantity the NCCL all-reduce adds up."""
+    from plate_inverse_problem_b200 import _lib
+    prob = small.problem()
+    F = 9
+    freqs = np.linspace(40.0, 600.0, F)
+    ref = small.op.forward(freqs, PARAMS) * 1.07
+    L, g = prob.getLossFunction(freqs, ref, "MSE_LOG_AFC").value_and_grad(PARAMS)
+    st = prob._st
+    acc = np.zeros(1 + PARAMS.size)
+    for lo, hi in ((0, 4), (4, 9)):
+        coef, s, dc, ds = prob.coefficients(freqs[lo:hi], PARAMS, with_jacobian=True)
+        n = hi - lo
+        fr, ls = np.zeros(n), np.zeros(1)
+        ct, cts = np.zeros((n, 26), dtype=np.complex128), np.zeros(n, dtype=np.complex128)
+        st.check(st.lib.jpb_eval_loss_grad(st.h, prob.solver_num, n, _lib.ptr(np.ascontiguousarray(coef)),
+                                           _lib.ptr(np.ascontiguousarray(s)),
+                                           _lib.ptr(np.ascontiguousarray(ref[lo:hi])), _lib.ptr(prob.weights),
+                                           3, F, _lib.ptr(fr), _lib.ptr(ls), _lib.ptr(ct), _lib.ptr(cts), None))
+        acc[0] += ls[0] / F
+        acc[1:] += np.real(np.einsum("fk,fkp->p", ct, dc) + np.einsum("f,fp->p", cts, ds))
+    assert abs(acc[0] - L) <= 1e-12 * abs(L)
+    assert relerr(acc[1:], g) <= 1e-10
