@@ -57,6 +57,11 @@ const char* jpb_last_error(const jpb_state* st);
 int jpb_set_memory_budget(jpb_state* st, int64_t bytes);
 /* iterative-refinement steps applied after every triangular solve (default 1) */
 int jpb_set_refinement(jpb_state* st, int steps);
+/* number of concurrent sub-waves (CUDA streams) a fused evaluation is cut into (default 1;
+ * 1 = strictly sequential phases, which is what the per-phase timers of jpb_last_timings
+ * need to be meaningful).  No counterpart in the reference (OpenMP over items,
+ * InnerState.h:277, is its analogue). */
+int jpb_set_streams(jpb_state* st, int n);
 
 /* ---- pattern registration (InnerState::add_mat) ------------------------------------
  * indices/indptr: CSC of the N x N pattern; indices_T/indptr_T/perm: the reference's CSR

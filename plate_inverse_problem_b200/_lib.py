@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libjaxplate_b200.so")
+# JPB_LIB_PATH: development override to load an alternative build of the same library
+LIB_PATH = os.environ.get("JPB_LIB_PATH") or os.path.join(_HERE, "libjaxplate_b200.so")
 
 JPB_OK, JPB_EINVAL, JPB_ECUDA, JPB_ESINGULAR, JPB_ENOMEM, JPB_ESTATE = range(6)
 LOSS_TYPES = {"MSE": 0, "RMSE": 1, "MSE_AFC": 2, "MSE_LOG_AFC": 3}
@@ -20,6 +21,7 @@ LOSS_TYPES = {"MSE": 0, "RMSE": 1, "MSE_AFC": 2, "MSE_LOG_AFC": 3}
 # every symbol include/jax_plate_b200.h declares
 EXPORTED_SYMBOLS = (
     "jpb_create", "jpb_destroy", "jpb_last_error", "jpb_set_memory_budget", "jpb_set_refinement",
+    "jpb_set_streams",
     "jpb_add_mat", "jpb_symbolic_info", "jpb_get_ordering", "jpb_solve", "jpb_matvec",
     "jpb_assemble", "jpb_register_components", "jpb_eval_forward", "jpb_eval_loss_grad",
     "jpb_eval_loss_grad_dev", "jpb_last_timings", "jpb_dmma_peak", "jpb_selftest",
@@ -47,6 +49,7 @@ def load_library() -> C.CDLL:
     lib.jpb_last_error.restype = C.c_char_p
     lib.jpb_set_memory_budget.argtypes = [vp, i64]
     lib.jpb_set_refinement.argtypes = [vp, i32]
+    lib.jpb_set_streams.argtypes = [vp, i32]
     lib.jpb_add_mat.argtypes = [vp, i64, i64, dp, dp, dp, dp, dp, i32, C.POINTER(i32)]
     lib.jpb_symbolic_info.argtypes = [vp, i32, dp]
     lib.jpb_get_ordering.argtypes = [vp, i32, dp]

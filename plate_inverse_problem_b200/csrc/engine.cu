@@ -85,6 +85,14 @@ struct Pattern {
     std::vector<int> levelptr;
     // fronts of a level are sorted by order, largest first; cls[l] = {#big, #mid} (rest small)
     std::vector<std::array<int, 2>> cls;
+    // launch groups of the numeric factorisation, per level: a run of the (size-sorted)
+    // front list handled by one kernel instantiation
+    struct FactorGroup {
+        int first, count;   // into the level's front list
+        int smem;           // 0: front stays in global memory; else dynamic shared bytes
+        int nt;
+    };
+    std::vector<std::vector<FactorGroup>> fgroups;
     // symbolic data on the device
     FrontDesc* d_fr = nullptr;
     int *d_rowidx_orig = nullptr, *d_children = nullptr, *d_relmap = nullptr, *d_ent_src = nullptr,
@@ -132,8 +140,19 @@ struct jpb_state {
     double launches = 0;
     double wave = 0;
     bool timing = true;
+    int nstreams = 1;                  // sub-waves of a fused evaluation run concurrently
+    std::vector<cudaStream_t> aux;
 
+    void ensure_streams(int n) {
+        while ((int)aux.size() < n) {
+            cudaStream_t q;
+            if (cudaStreamCreateWithFlags(&q, cudaStreamNonBlocking) != cudaSuccess)
+                throw std::runtime_error("cudaStreamCreate failed");
+            aux.push_back(q);
+        }
+    }
     ~jpb_state() {
+        for (auto q : aux) cudaStreamDestroy(q);
         for (auto e : pool) cudaEventDestroy(e);
         if (stream) cudaStreamDestroy(stream);
     }
@@ -221,6 +240,10 @@ void launch_check(jpb_state* st) {
 struct Tuning {
     int front_big = 128, front_mid = 64;
     int nt[3] = {256, 128, 64};
+    // shared-memory-resident fronts: order bound and CTA width of each class, ascending
+    int smem_max = 112;
+    int sbound[5] = {32, 48, 64, 80, 112};
+    int snt[5] = {64, 64, 128, 128, 256};
     Tuning() {
         auto geti = [](const char* name, int def) {
             const char* v = getenv(name);
@@ -233,8 +256,30 @@ struct Tuning {
         nt[2] = geti("JPB_NT_SMALL", nt[2]);
         for (int& v : nt)
             if (v != 64 && v != 128 && v != 256) v = 128;
+        smem_max = geti("JPB_SMEM_MAX", smem_max);
+        if (smem_max > 112) smem_max = 112;
+        sbound[4] = std::max(smem_max, 81);
+        const char* names[5] = {"JPB_SNT0", "JPB_SNT1", "JPB_SNT2", "JPB_SNT3", "JPB_SNT4"};
+        for (int c = 0; c < 5; ++c) {
+            snt[c] = geti(names[c], snt[c]);
+            if (snt[c] != 64 && snt[c] != 128 && snt[c] != 256) snt[c] = 128;
+        }
     }
 };
+// symbolic options, overridable for tuning runs (JPB_LEAF, JPB_RELAX_SMALL, ...)
+SymbolicOptions symbolic_options() {
+    SymbolicOptions o;
+    auto geti = [](const char* name, int def) { const char* v = getenv(name); return v ? atoi(v) : def; };
+    auto getd = [](const char* name, double def) { const char* v = getenv(name); return v ? atof(v) : def; };
+    o.leaf_size = geti("JPB_LEAF", o.leaf_size);
+    o.relax_small = geti("JPB_RELAX_SMALL", o.relax_small);
+    o.relax_mid = geti("JPB_RELAX_MID", o.relax_mid);
+    o.relax_mid_frac = getd("JPB_RELAX_MID_FRAC", o.relax_mid_frac);
+    o.relax_big = geti("JPB_RELAX_BIG", o.relax_big);
+    o.relax_big_frac = getd("JPB_RELAX_BIG_FRAC", o.relax_big_frac);
+    o.relax_any_frac = getd("JPB_RELAX_ANY_FRAC", o.relax_any_frac);
+    return o;
+}
 const Tuning& tuning() {
     static Tuning t;
     return t;
@@ -274,14 +319,27 @@ void factor(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* F, const cd
             int* status) {
     Span span(st, s, PH_FACTOR);
     for (int l = 0; l < P.S.nlevels; ++l) {
-        for_each_class(st, P, l, nsys, [&](int c, const int* lf, unsigned grid) {
-#define JPB_FACTOR(NT)                                                                          \
-    if (ent_order) factor_level_kernel<true, NT><<<grid, NT, 0, s>>>(P.sd, lf, nsys, F, data, status); \
-    else factor_level_kernel<false, NT><<<grid, NT, 0, s>>>(P.sd, lf, nsys, F, data, status);
-            const int nt = tuning().nt[c];
-            if (nt == 256) { JPB_FACTOR(256) } else if (nt == 128) { JPB_FACTOR(128) } else { JPB_FACTOR(64) }
+        const int* lfl = P.d_levelfronts + P.levelptr[l];
+        for (const Pattern::FactorGroup& g : P.fgroups[l]) {
+            const int64_t grid64 = (int64_t)g.count * nsys;
+            if (grid64 > 0x7fffffff) throw InvalidArg("wave too large for one launch");
+            const unsigned grid = (unsigned)grid64;
+            const int* lf = lfl + g.first;
+#define JPB_FACTOR(KERNEL, NT)                                                                       \
+    if (ent_order) KERNEL<true, NT><<<grid, NT, g.smem, s>>>(P.sd, lf, nsys, F, data, status);       \
+    else KERNEL<false, NT><<<grid, NT, g.smem, s>>>(P.sd, lf, nsys, F, data, status);
+            if (g.smem) {
+                if (g.nt == 256) { JPB_FACTOR(factor_smem_kernel, 256) }
+                else if (g.nt == 128) { JPB_FACTOR(factor_smem_kernel, 128) }
+                else { JPB_FACTOR(factor_smem_kernel, 64) }
+            } else {
+                if (g.nt == 256) { JPB_FACTOR(factor_level_kernel, 256) }
+                else if (g.nt == 128) { JPB_FACTOR(factor_level_kernel, 128) }
+                else { JPB_FACTOR(factor_level_kernel, 64) }
+            }
 #undef JPB_FACTOR
-        });
+            launch_check(st);
+        }
     }
 }
 
@@ -400,49 +458,88 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
     if (loss_sum) CK(cudaMemsetAsync(loss_sum, 0, sizeof(double), s));
     if (status) CK(cudaMemsetAsync(status, 0, sizeof(int) * B, s));
 
+    // One pipeline (assemble -> factor -> solve -> read-out [-> loss -> adjoint solve -> gradient])
+    // over the systems [g0, g0 + n) of the batch, which sit at [l0, l0 + n) of the wave buffers.
+    auto run_chunk = [&](cudaStream_t sc, int64_t g0, int64_t l0, int n) {
+        cd* Fc = F + l0 * P.S.front_slots;
+        cd* valsc = vals + l0 * nnz;
+        cd* Vc = V + l0 * P.S.vec_slots;
+        cd *vbc = vb + l0 * N, *vxc = vx + l0 * N, *vrc = vr + l0 * N, *vdc = vd + l0 * N,
+           *vlamc = vlam + l0 * N;
+        {
+            Span span(st, sc, PH_FACTOR);
+            assemble_entries(st, sc, P, n, coef + g0 * K, valsc);
+        }
+        factor(st, sc, P, n, Fc, valsc, true, status ? status + g0 : nullptr);
+        {
+            dim3 grid((N + 255) / 256, n);
+            scale_rhs_kernel<<<grid, 256, 0, sc>>>(N, P.d_rhs_vec, scale + g0, vbc);
+            launch_check(st);
+        }
+        solve_refined(st, sc, P, Fc, false, valsc, 1, true, vbc, 1, n, vxc, Vc, vrc, vdc, n, 1, PH_FWD);
+        {
+            Span span(st, sc, PH_READOUT);
+            readout_kernel<<<n, 256, 0, sc>>>(N, R, P.d_Q, vxc, y + g0 * R);
+            launch_check(st);
+            if (u_out) CK(cudaMemcpyAsync(u_out + g0 * N, vxc, (size_t)n * N * 16, cudaMemcpyDeviceToDevice, sc));
+        }
+        if (!adjoint) return;
+        {
+            Span span(st, sc, PH_READOUT);
+            loss_kernel<<<(n + 127) / 128, 128, 0, sc>>>(n, R, y + g0 * R, w, ref + g0, loss_type,
+                                                         1.0 / (double)F_total, fr + g0, loss_term + l0,
+                                                         ybar + l0 * R);
+            launch_check(st);
+            dim3 grid((N + 255) / 256, n);
+            cotangent_kernel<<<grid, 256, 0, sc>>>(N, R, P.d_Q, ybar + l0 * R, vbc);
+            launch_check(st);
+        }
+        solve_refined(st, sc, P, Fc, true, valsc, 1, true, vbc, 1, n, vlamc, Vc, vrc, vdc, n, 1, PH_ADJ);
+        {
+            Span span(st, sc, PH_GRAD);
+            const int ngroups = (n + GRAD_SYS - 1) / GRAD_SYS;
+            cd* part = partial + nchunks * l0 * K;
+            grad_kernel<<<(unsigned)(nchunks * ngroups), GRAD_THREADS, GRAD_SMEM, sc>>>(
+                nnz, N, K, P.d_csc_row, P.d_csc_col, P.d_mats, vlamc, vxc, part, n, ngroups);
+            launch_check(st);
+            int64_t nbk = (int64_t)n * K;
+            grad_reduce_kernel<<<(unsigned)((nbk + 127) / 128), 128, 0, sc>>>((int)nchunks, nbk, part,
+                                                                              ct_coef + g0 * K);
+            launch_check(st);
+            readout_kernel<<<n, 256, 0, sc>>>(N, 1, P.d_rhs_vec, vlamc, ct_s + g0);
+            launch_check(st);
+        }
+    };
+
+    // The systems of a wave are independent, so a wave is cut into `nstreams` sub-waves that run
+    // the whole pipeline on their own streams: the narrow launches near the root of the
+    // elimination tree (a few hundred CTAs, long pivot chains) and the bandwidth-bound solve
+    // sweeps of one sub-wave fill the SMs the others leave idle.
     for (int64_t b0 = 0; b0 < B; b0 += W) {
         const int nw = (int)std::min<int64_t>(W, B - b0);
-        {
-            Span span(st, s, PH_FACTOR);
-            assemble_entries(st, s, P, nw, coef + b0 * K, vals);
+        const int ns = (int)std::max<int64_t>(1, std::min<int64_t>(st->nstreams, nw / 32));
+        if (ns == 1) {
+            run_chunk(s, b0, 0, nw);
+        } else {
+            st->ensure_streams(ns - 1);
+            cudaEvent_t fork = st->ev();
+            CK(cudaEventRecord(fork, s));
+            const int per = (nw + ns - 1) / ns;
+            for (int c = 0; c < ns; ++c) {
+                const int l0 = c * per, n = std::min(per, nw - l0);
+                if (n <= 0) break;
+                cudaStream_t sc = c == 0 ? s : st->aux[c - 1];
+                if (c > 0) CK(cudaStreamWaitEvent(sc, fork, 0));
+                run_chunk(sc, b0 + l0, l0, n);
+                if (c > 0) {
+                    cudaEvent_t join = st->ev();
+                    CK(cudaEventRecord(join, sc));
+                    CK(cudaStreamWaitEvent(s, join, 0));
+                }
+            }
         }
-        factor(st, s, P, nw, F, vals, true, status ? status + b0 : nullptr);
-        {
-            dim3 grid((N + 255) / 256, nw);
-            scale_rhs_kernel<<<grid, 256, 0, s>>>(N, P.d_rhs_vec, scale + b0, vb);
-            launch_check(st);
-        }
-        solve_refined(st, s, P, F, false, vals, 1, true, vb, 1, nw, vx, V, vr, vd, nw, 1, PH_FWD);
-        {
-            Span span(st, s, PH_READOUT);
-            readout_kernel<<<nw, 256, 0, s>>>(N, R, P.d_Q, vx, y + b0 * R);
-            launch_check(st);
-            if (u_out) CK(cudaMemcpyAsync(u_out + b0 * N, vx, (size_t)nw * N * 16, cudaMemcpyDeviceToDevice, s));
-        }
-        if (!adjoint) continue;
-        {
-            Span span(st, s, PH_READOUT);
-            loss_kernel<<<(nw + 127) / 128, 128, 0, s>>>(nw, R, y + b0 * R, w, ref + b0, loss_type,
-                                                         1.0 / (double)F_total, fr + b0, loss_term, ybar);
-            launch_check(st);
+        if (adjoint) {
             sum_kernel<<<1, 256, 0, s>>>(nw, loss_term, loss_sum);
-            launch_check(st);
-            dim3 grid((N + 255) / 256, nw);
-            cotangent_kernel<<<grid, 256, 0, s>>>(N, R, P.d_Q, ybar, vb);
-            launch_check(st);
-        }
-        solve_refined(st, s, P, F, true, vals, 1, true, vb, 1, nw, vlam, V, vr, vd, nw, 1, PH_ADJ);
-        {
-            Span span(st, s, PH_GRAD);
-            const int ngroups = (nw + GRAD_SYS - 1) / GRAD_SYS;
-            grad_kernel<<<(unsigned)(nchunks * ngroups), GRAD_THREADS, GRAD_SMEM, s>>>(
-                nnz, N, K, P.d_csc_row, P.d_csc_col, P.d_mats, vlam, vx, partial, nw, ngroups);
-            launch_check(st);
-            int64_t nbk = (int64_t)nw * K;
-            grad_reduce_kernel<<<(unsigned)((nbk + 127) / 128), 128, 0, s>>>((int)nchunks, nbk, partial,
-                                                                             ct_coef + b0 * K);
-            launch_check(st);
-            readout_kernel<<<nw, 256, 0, s>>>(N, 1, P.d_rhs_vec, vlam, ct_s + b0);
             launch_check(st);
         }
     }
@@ -461,11 +558,25 @@ int jpb_create(jpb_state** out, int device) {
     if (e != cudaSuccess || n <= 0 || device < 0 || device >= n) return JPB_ECUDA;
     auto st = std::make_unique<jpb_state>();
     st->device = device;
+    if (const char* v = getenv("JPB_STREAMS")) st->nstreams = std::max(1, std::min(16, atoi(v)));
     if (cudaSetDevice(device) != cudaSuccess) return JPB_ECUDA;
     if (cudaStreamCreateWithFlags(&st->stream, cudaStreamNonBlocking) != cudaSuccess) return JPB_ECUDA;
     if (cudaFuncSetAttribute(grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GRAD_SMEM) !=
         cudaSuccess)
         return JPB_ECUDA;
+    {
+        const int smem_cap = 112 * smem_ld(112) * (int)sizeof(cd);
+        bool ok = true;
+        auto set = [&](auto kernel) {
+            ok &= cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap) == cudaSuccess;
+            ok &= cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                       cudaSharedmemCarveoutMaxShared) == cudaSuccess;
+        };
+        set(factor_smem_kernel<true, 256>); set(factor_smem_kernel<false, 256>);
+        set(factor_smem_kernel<true, 128>); set(factor_smem_kernel<false, 128>);
+        set(factor_smem_kernel<true, 64>); set(factor_smem_kernel<false, 64>);
+        if (!ok) return JPB_ECUDA;
+    }
     *out = st.release();
     return JPB_OK;
 }
@@ -482,6 +593,12 @@ const char* jpb_last_error(const jpb_state* st) { return st ? st->err.c_str() : 
 int jpb_set_memory_budget(jpb_state* st, int64_t bytes) {
     if (!st || bytes < 0) return JPB_EINVAL;
     st->budget = bytes;
+    return JPB_OK;
+}
+
+int jpb_set_streams(jpb_state* st, int n) {
+    if (!st || n < 1 || n > 16) return fail(st, JPB_EINVAL, "streams must be in [1, 16]");
+    st->nstreams = n;
     return JPB_OK;
 }
 
@@ -517,8 +634,7 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
         }
     }
     auto P = std::make_unique<Pattern>();
-    SymbolicOptions opt;
-    analyze((int)N, ap.data(), ai.data(), opt, P->S);
+    analyze((int)N, ap.data(), ai.data(), symbolic_options(), P->S);
     Symbolic& S = P->S;
 
     // CSR view (exact transpose of the CSC pattern) with CSR->CSC positions
@@ -584,6 +700,36 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
             else if (sz > FRONT_MID) ++nmid;
         }
         P->cls[l] = {nbig, nmid};
+    }
+    // factor launch groups: fronts of a level are sorted largest first
+    P->fgroups.assign(S.nlevels, {});
+    {
+        const Tuning& tn = tuning();
+        auto group_of = [&](int sz, int& nt) {      // class id: 0..2 global, 3.. shared
+            if (sz > tn.smem_max) {
+                int c = sz > tn.front_big ? 0 : (sz > tn.front_mid ? 1 : 2);
+                nt = tn.nt[c];
+                return c;
+            }
+            int c = 0;
+            while (c < 4 && sz > tn.sbound[c]) ++c;
+            nt = tn.snt[c];
+            return 3 + (4 - c);
+        };
+        for (int l = 0; l < S.nlevels; ++l) {
+            int prev = -1;
+            for (int q = S.levelptr[l]; q < S.levelptr[l + 1]; ++q) {
+                const int sz = S.f_s[S.levelfronts[q]];
+                int nt = 0;
+                const int c = group_of(sz, nt);
+                if (c != prev) {
+                    const int smem = c >= 3 ? sz * smem_ld(sz) * (int)sizeof(cd) : 0;
+                    P->fgroups[l].push_back({q - S.levelptr[l], 0, smem, nt});
+                    prev = c;
+                }
+                P->fgroups[l].back().count++;
+            }
+        }
     }
     P->d_fr = upload(fr);
     P->d_rowidx_orig = upload(S.rowidx_orig);
@@ -1036,7 +1182,7 @@ int jpb_host_analyze(int64_t N, int64_t nnz, const void* indices, const void* in
         for (int64_t i = 0; i < nnz; ++i) ai[i] = get(indices, i);
         if (ap[0] != 0 || ap[N] != nnz) throw std::runtime_error("host_analyze: indptr does not match nnz");
         auto h = std::make_unique<jpb_host_symbolic>();
-        analyze((int)N, ap.data(), ai.data(), SymbolicOptions(), h->S);
+        analyze((int)N, ap.data(), ai.data(), symbolic_options(), h->S);
         *out = h.release();
         return JPB_OK;
     } catch (const std::exception& e) {

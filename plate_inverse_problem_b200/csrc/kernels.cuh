@@ -86,67 +86,92 @@ struct Acc {
 };
 
 // acc += A[0:8MB, 0:K] * B[0:K, 0:8NB];  A(i,p) = A[i*lda + p] valid for i < mrows,
-// B(p,j) = B[p*ldb + j] valid for j < ncols; anything outside reads as zero.
+// B(p,j) = B[p*ldb + j] valid for j < ncols (mrows, ncols >= 1).
 // Fragment layout of mma.m8n8k4.f64: lane = 4*g + t holds A(g, t), B(t, g) and
 // C(g, 2t), C(g, 2t+1).  One 16-byte load per lane yields the re and im fragments.
+// Rows / columns past the edge are clamped onto the last valid one: they only feed
+// accumulator rows / columns that store_tile never writes, so the main loop carries no
+// predicates and advances plain pointers; only a K tail (K % 4) is masked.
+template <int MB, int NB>
+__device__ __forceinline__ void warp_mma_step(Acc<MB, NB>& acc, const cd (&a)[MB], const cd (&b)[NB]) {
+#pragma unroll
+    for (int m = 0; m < MB; ++m)
+#pragma unroll
+        for (int n = 0; n < NB; ++n) dmma(acc.re[m][n][0], acc.re[m][n][1], a[m].x, b[n].x);
+#pragma unroll
+    for (int m = 0; m < MB; ++m)
+#pragma unroll
+        for (int n = 0; n < NB; ++n) dmma(acc.im[m][n][0], acc.im[m][n][1], a[m].x, b[n].y);
+#pragma unroll
+    for (int m = 0; m < MB; ++m)
+#pragma unroll
+        for (int n = 0; n < NB; ++n) dmma(acc.re[m][n][0], acc.re[m][n][1], -a[m].y, b[n].y);
+#pragma unroll
+    for (int m = 0; m < MB; ++m)
+#pragma unroll
+        for (int n = 0; n < NB; ++n) dmma(acc.im[m][n][0], acc.im[m][n][1], a[m].y, b[n].x);
+}
+
 template <int MB, int NB>
 __device__ __forceinline__ void warp_gemm(Acc<MB, NB>& acc, const cd* A, int lda, int mrows,
                                           const cd* B, int ldb, int ncols, int K, int lane) {
     const int g = lane >> 2, t = lane & 3;
-    const cd* ap[MB];
-    const cd* bp[NB];
-    bool aok[MB], bok[NB];
+    const cd* pa[MB];
+    const cd* pb[NB];
 #pragma unroll
-    for (int m = 0; m < MB; ++m) {
-        int i = 8 * m + g;
-        aok[m] = i < mrows;
-        ap[m] = A + (int64_t)i * lda + t;
-    }
+    for (int m = 0; m < MB; ++m) pa[m] = A + (int64_t)min(8 * m + g, mrows - 1) * lda + t;
 #pragma unroll
-    for (int n = 0; n < NB; ++n) {
-        int j = 8 * n + g;
-        bok[n] = j < ncols;
-        bp[n] = B + (int64_t)t * ldb + j;
-    }
-    const cd zero = make_double2(0.0, 0.0);
+    for (int n = 0; n < NB; ++n) pb[n] = B + (int64_t)t * ldb + min(8 * n + g, ncols - 1);
+    const int64_t bstep = 4 * (int64_t)ldb;
+    const int nfull = K >> 2;
     cd a[MB], b[NB];
-    {
-        bool pk = t < K;
+    if (nfull > 0) {
 #pragma unroll
-        for (int m = 0; m < MB; ++m) a[m] = (pk && aok[m]) ? ap[m][0] : zero;
+        for (int m = 0; m < MB; ++m) a[m] = *pa[m];
 #pragma unroll
-        for (int n = 0; n < NB; ++n) b[n] = (pk && bok[n]) ? bp[n][0] : zero;
+        for (int n = 0; n < NB; ++n) b[n] = *pb[n];
     }
-    for (int p0 = 0; p0 < K; p0 += 4) {
+    // two k-steps per trip so that the operand sets ping-pong without register moves
+    int it = 1;
+#pragma unroll 1
+    for (; it + 1 < nfull; it += 2) {
         cd an[MB], bn[NB];
-        {
-            const int p1 = p0 + 4;
-            bool pk = p1 + t < K;
 #pragma unroll
-            for (int m = 0; m < MB; ++m) an[m] = (pk && aok[m]) ? ap[m][p1] : zero;
+        for (int m = 0; m < MB; ++m) { pa[m] += 4; an[m] = *pa[m]; }
 #pragma unroll
-            for (int n = 0; n < NB; ++n) bn[n] = (pk && bok[n]) ? bp[n][(int64_t)p1 * ldb] : zero;
-        }
+        for (int n = 0; n < NB; ++n) { pb[n] += bstep; bn[n] = *pb[n]; }
+        warp_mma_step<MB, NB>(acc, a, b);
 #pragma unroll
-        for (int m = 0; m < MB; ++m)
+        for (int m = 0; m < MB; ++m) { pa[m] += 4; a[m] = *pa[m]; }
 #pragma unroll
-            for (int n = 0; n < NB; ++n) dmma(acc.re[m][n][0], acc.re[m][n][1], a[m].x, b[n].x);
+        for (int n = 0; n < NB; ++n) { pb[n] += bstep; b[n] = *pb[n]; }
+        warp_mma_step<MB, NB>(acc, an, bn);
+    }
+    if (it < nfull) {
+        cd an[MB], bn[NB];
 #pragma unroll
-        for (int m = 0; m < MB; ++m)
+        for (int m = 0; m < MB; ++m) { pa[m] += 4; an[m] = *pa[m]; }
 #pragma unroll
-            for (int n = 0; n < NB; ++n) dmma(acc.im[m][n][0], acc.im[m][n][1], a[m].x, b[n].y);
-#pragma unroll
-        for (int m = 0; m < MB; ++m)
-#pragma unroll
-            for (int n = 0; n < NB; ++n) dmma(acc.re[m][n][0], acc.re[m][n][1], -a[m].y, b[n].y);
-#pragma unroll
-        for (int m = 0; m < MB; ++m)
-#pragma unroll
-            for (int n = 0; n < NB; ++n) dmma(acc.im[m][n][0], acc.im[m][n][1], a[m].y, b[n].x);
+        for (int n = 0; n < NB; ++n) { pb[n] += bstep; bn[n] = *pb[n]; }
+        warp_mma_step<MB, NB>(acc, a, b);
 #pragma unroll
         for (int m = 0; m < MB; ++m) a[m] = an[m];
 #pragma unroll
         for (int n = 0; n < NB; ++n) b[n] = bn[n];
+    }
+    const int rem = K & 3;
+    if (rem) {      // K tail: both operands masked (0 * garbage could be NaN)
+        cd an[MB], bn[NB];
+        const cd zero = make_double2(0.0, 0.0);
+        const int64_t adv = nfull > 0 ? 4 : 0;
+#pragma unroll
+        for (int m = 0; m < MB; ++m) an[m] = t < rem ? pa[m][adv] : zero;
+#pragma unroll
+        for (int n = 0; n < NB; ++n) bn[n] = t < rem ? pb[n][adv * ldb] : zero;
+        if (nfull > 0) warp_mma_step<MB, NB>(acc, a, b);
+        warp_mma_step<MB, NB>(acc, an, bn);
+    } else if (nfull > 0) {
+        warp_mma_step<MB, NB>(acc, a, b);
     }
 }
 
@@ -188,85 +213,91 @@ struct TileSmem {
     int piv[TW];
     int src[TW];
     int sing;
+    int swapped;
 };
+
+// pivot row of column p among rows p..n-1 of the tile T (leading dimension ldt): argmax of
+// max(|re|, |im|), compared on the upper 27 bits of the double (sign-free exponent + 16
+// mantissa bits: ample for a pivot choice) so that one integer warp reduction does the
+// search; ties go to the lowest row.  Returns the key (0 in its upper bits: no usable pivot).
+__device__ __forceinline__ unsigned pivot_search(const cd* T, int ldt, int n, int p, int lane) {
+    unsigned key = 0u;
+    if (lane >= p && lane < n) {
+        const cd v = T[lane * ldt + p];
+        const double m = fmax(fabs(v.x), fabs(v.y));
+        const unsigned hi = (unsigned)__double2hiint(m);
+        if (m == m && hi < 0x7ff00000u) key = ((hi >> 4) << 5) | (unsigned)(31 - lane);
+    }
+    return __reduce_max_sync(0xffffffffu, key);
+}
+// 1/z = conj(z) / |z|^2 after scaling z by 2^-e (e = exponent carried by the search key) to
+// dodge over/underflow: one division
+__device__ __forceinline__ cd pivot_reciprocal(cd z, unsigned key) {
+    const int ex = ((int)(key >> 21)) - 1023;
+    const double sc = __hiloint2double((1023 - ex) << 20, 0);   // 2^-ex, exact
+    const double zx = z.x * sc, zy = z.y * sc;
+    const double q = sc / fma(zx, zx, zy * zy);
+    return make_double2(zx * q, -zy * q);
+}
 
 // Gauss-Jordan inversion of the n x n block in ts.D[0] with partial pivoting restricted to
 // the block (row exchanges only move rows inside the pivot tile, so the static front
 // structure is unaffected: D^-1 absorbs the permutation).  Double buffered: step p reads
 // D[cur] and writes D[cur^1], so one barrier per step suffices; every warp finds the pivot
-// row redundantly with shuffles.  Returns the buffer index holding D^-1.  A zero /
+// row redundantly.  A thread owns column j = lane of the rows its warp strides over, so the
+// normalised pivot-row element is formed once per step and an element update is two shared
+// loads, four FMAs and a store.  Returns the buffer index holding D^-1.  A zero /
 // non-finite pivot sets ts.sing.  All NT threads of the CTA take part.
 template <int NT>
 __device__ __forceinline__ int invert_tile(TileSmem& ts, int n, int tid) {
-    const int lane = tid & 31;
+    const int lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = NT / 32;
     int cur = 0;
     for (int p = 0; p < n; ++p) {
-        cd (*Dc)[TLD] = ts.D[cur];
-        cd (*Dn)[TLD] = ts.D[cur ^ 1];
-        // pivot row = argmax over rows >= p of max(|re|, |im|), compared on the upper 27 bits
-        // of the double (sign-free exponent + 16 mantissa bits: ample for a pivot choice)
-        // so that one integer warp reduction does the search; ties go to the lowest row.
-        unsigned key = 0u;
-        if (lane >= p && lane < n) {
-            const cd v = Dc[lane][p];
-            const double m = fmax(fabs(v.x), fabs(v.y));
-            const unsigned hi = (unsigned)__double2hiint(m);
-            if (m == m && hi < 0x7ff00000u) key = ((hi >> 4) << 5) | (unsigned)(31 - lane);
-        }
-        key = __reduce_max_sync(0xffffffffu, key);
+        const cd* Dc = &ts.D[cur][0][0];
+        cd* Dn = &ts.D[cur ^ 1][0][0];
+        const unsigned key = pivot_search(Dc, TLD, n, p, lane);
         const bool ok = (key >> 5) != 0u;
         const int r = ok ? 31 - (int)(key & 31u) : p;
         if (tid == 0) {
             ts.piv[p] = r;
             if (!ok) ts.sing = 1;
+            if (r != p) ts.swapped = 1;
         }
-        cd d = make_double2(1.0, 0.0);
-        if (ok) {
-            // 1/z = conj(z) / |z|^2 after scaling z by 2^-e to dodge over/underflow: one division
-            const cd z = Dc[r][p];
-            const int ex = ((int)(key >> 21)) - 1023;          // exponent of max(|re|, |im|)
-            const double sc = __hiloint2double((1023 - ex) << 20, 0);   // 2^-ex, exact
-            const double zx = z.x * sc, zy = z.y * sc;
-            const double q = sc / fma(zx, zx, zy * zy);
-            d = make_double2(zx * q, -zy * q);
-        }
-        for (int e = tid; e < n * TW; e += NT) {
-            const int i = e >> 5, j = e & 31;
-            if (j >= n) continue;
-            const cd rb = (j == p) ? d : cmul(Dc[r][j], d);
-            cd out;
-            if (i == p) {
-                out = rb;
-            } else {
-                const int oi = (i == r) ? p : i;     // rows p and r trade places
-                const cd f = Dc[oi][p];
-                out = (j == p) ? make_double2(0.0, 0.0) : Dc[oi][j];
-                out.x = fma(-f.x, rb.x, out.x); out.x = fma(f.y, rb.y, out.x);
-                out.y = fma(-f.x, rb.y, out.y); out.y = fma(-f.y, rb.x, out.y);
+        const cd d = ok ? pivot_reciprocal(Dc[r * TLD + p], key) : make_double2(1.0, 0.0);
+        if (lane < n) {
+            const cd rb = (lane == p) ? d : cmul(Dc[r * TLD + lane], d);
+            for (int i = warp; i < n; i += NW) {
+                cd out = rb;
+                if (i != p) {
+                    const int oi = (i == r) ? p : i;     // rows p and r trade places
+                    const cd f = Dc[oi * TLD + p];
+                    out = Dc[oi * TLD + lane];
+                    if (lane == p) out = make_double2(0.0, 0.0);
+                    out.x = fma(-f.x, rb.x, out.x); out.x = fma(f.y, rb.y, out.x);
+                    out.y = fma(-f.x, rb.y, out.y); out.y = fma(-f.y, rb.x, out.y);
+                }
+                Dn[i * TLD + lane] = out;
             }
-            Dn[i][j] = out;
         }
         __syncthreads();
         cur ^= 1;
     }
     // undo the row exchanges: A^-1 = B P  <=>  column j of the result is column src[j] of B
-    if (tid == 0) {
-        bool any = false;
-        for (int j = 0; j < n; ++j) { ts.src[j] = j; any |= ts.piv[j] != j; }
-        for (int p = n - 1; p >= 0; --p) {
-            int r = ts.piv[p], t = ts.src[p];
-            ts.src[p] = ts.src[r];
-            ts.src[r] = t;
-        }
-        ts.piv[0] = any ? -1 : 0;     // flag: permutation is not the identity
-    }
-    __syncthreads();
-    if (ts.piv[0] < 0) {
-        for (int e = tid; e < n * TW; e += NT) {
-            const int i = e >> 5, j = e & 31;
-            if (j < n) ts.D[cur ^ 1][i][j] = ts.D[cur][i][ts.src[j]];
+    if (ts.swapped) {      // uniform: last written before the final barrier of the loop
+        if (tid == 0) {
+            for (int j = 0; j < n; ++j) ts.src[j] = j;
+            for (int p = n - 1; p >= 0; --p) {
+                int r = ts.piv[p], t = ts.src[p];
+                ts.src[p] = ts.src[r];
+                ts.src[r] = t;
+            }
         }
         __syncthreads();
+        if (lane < n)
+            for (int i = warp; i < n; i += NW) ts.D[cur ^ 1][i][lane] = ts.D[cur][i][ts.src[lane]];
+        __syncthreads();
+        if (tid == 0) ts.swapped = 0;
         cur ^= 1;
     }
     return cur;
@@ -280,13 +311,20 @@ constexpr int KMAX = 32;   // component matrices supported by the fused assembly
 //   FUSED = true : A entries are sum_k coef[b,k] * mats_f[k, q]  (mats_f in front-entry order),
 //                  also stored to vals[b, q] for the residual kernels
 //   FUSED = false: A entries are data[b, ent_src[q]]
+#ifndef JPB_WN
+#define JPB_WN 4
+#endif
+#ifndef JPB_OCC
+#define JPB_OCC 512
+#endif
 template <bool ENT_ORDER, int NT>
-__global__ void __launch_bounds__(NT, 512 / NT)
+__global__ void __launch_bounds__(NT, JPB_OCC / NT)
 factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd* Fall,
                     const cd* __restrict__ data, int* status) {
     __shared__ TileSmem ts;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = NT / 32;
+    constexpr int WN = JPB_WN, WC = 8 * WN;   // warp tile: 16 rows x WC columns
     constexpr int FACTOR_THREADS = NT;
     const int b = blockIdx.x % nsys;
     const FrontDesc fd = sd.fr[level_fronts[blockIdx.x / nsys]];
@@ -294,7 +332,7 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
     cd* F = Fsys + fd.off;
     const int s = fd.s, k = fd.k, ld = fd.ld;
 
-    if (tid == 0) ts.sing = 0;
+    if (tid == 0) { ts.sing = 0; ts.swapped = 0; }
     // ---- zero, then A entries (every entry owns its slot), then the children one by one
     {
         const cd zero = make_double2(0.0, 0.0);
@@ -355,23 +393,24 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
         const int j1 = j0 + jw;
         if (J > 0) {
             // column strip rows [j0,s) x cols [j0,j1) and row strip rows [j0,j1) x cols [j1,s)
-            const int nct = (s - j0 + 15) >> 4;
+            const int nct = ((s - j0 + 15) >> 4) * (TW / WC);
             const int nrr = (jw + 15) >> 4;
-            const int nrc = (s - j1 + 31) >> 5;
+            const int nrc = (s - j1 + WC - 1) / WC;
             const int ntiles = nct + nrr * nrc;
             for (int tile = warp; tile < ntiles; tile += NW) {
                 int r, c, mr, nc;
                 if (tile < nct) {
-                    r = j0 + 16 * tile; c = j0; mr = min(16, s - r); nc = jw;
+                    const int rt = tile / (TW / WC), ct = tile % (TW / WC);
+                    r = j0 + 16 * rt; c = j0 + WC * ct; mr = min(16, s - r); nc = min(WC, j1 - c);
                 } else {
                     int q = tile - nct;
-                    r = j0 + 16 * (q % nrr); c = j1 + 32 * (q / nrr);
-                    mr = min(16, j1 - r); nc = min(32, s - c);
+                    r = j0 + 16 * (q % nrr); c = j1 + WC * (q / nrr);
+                    mr = min(16, j1 - r); nc = min(WC, s - c);
                 }
-                Acc<2, 4> acc;
+                Acc<2, WN> acc;
                 acc.zero();
-                warp_gemm<2, 4>(acc, F + (int64_t)r * ld, ld, mr, F + c, ld, nc, j0, lane);
-                store_tile<2, 4, true>(acc, F + (int64_t)r * ld + c, ld, mr, nc, lane);
+                warp_gemm<2, WN>(acc, F + (int64_t)r * ld, ld, mr, F + c, ld, nc, j0, lane);
+                store_tile<2, WN, true>(acc, F + (int64_t)r * ld + c, ld, mr, nc, lane);
             }
             __syncthreads();
         }
@@ -387,17 +426,247 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
             if (j < jw) F[(int64_t)(j0 + i) * ld + j0 + j] = Dinv[i][j];
         }
         // Lt strip: rows [j1,s) x cols [j0,j1)  <-  F[rows, j0:j1] * D^-1
+        // (a warp owns whole rows of the strip: it reads them all before it stores any)
+        const int nlt = (s - j1 + 15) >> 4;
+        for (int tile = warp; tile < nlt; tile += NW) {
+            int r = j1 + 16 * tile, mr = min(16, s - r);
+            Acc<2, WN> acc[TW / WC];
+#pragma unroll
+            for (int h = 0; h < TW / WC; ++h) {
+                acc[h].zero();
+                if (WC * h < jw)
+                    warp_gemm<2, WN>(acc[h], F + (int64_t)r * ld + j0, ld, mr, &Dinv[0][WC * h], TLD,
+                                     jw - WC * h, jw, lane);
+            }
+#pragma unroll
+            for (int h = 0; h < TW / WC; ++h)
+                if (WC * h < jw)
+                    store_tile<2, WN, false>(acc[h], F + (int64_t)r * ld + j0 + WC * h, ld, mr, jw - WC * h, lane);
+        }
+        __syncthreads();
+    }
+    // ---- Schur complement of the contribution rows/cols
+    const int m = s - k;
+    if (m > 0 && k > 0) {
+        const int ntr = (m + 15) >> 4, ntc = (m + WC - 1) / WC;
+        for (int tile = warp; tile < ntr * ntc; tile += NW) {
+            int r = k + 16 * (tile % ntr), c = k + WC * (tile / ntr);
+            int mr = min(16, s - r), nc = min(WC, s - c);
+            Acc<2, WN> acc;
+            acc.zero();
+            warp_gemm<2, WN>(acc, F + (int64_t)r * ld, ld, mr, F + c, ld, nc, k, lane);
+            store_tile<2, WN, true>(acc, F + (int64_t)r * ld + c, ld, mr, nc, lane);
+        }
+    }
+    if (tid == 0 && ts.sing && status) atomicOr(status + b, 1);
+}
+
+// ------------------------------------------------- shared-memory-resident fronts (K2s)
+// Fronts whose s x s block fits the SM's shared memory never touch HBM between assembly and
+// the final store: zero fill, A entries, extend-add, pivot-tile inversion, the DMMA strip /
+// Lt / Schur updates all run on the shared copy, and the finished front (factors + Schur
+// block) leaves with one coalesced pass.  HBM traffic = the compulsory bytes only (entries
+// and child Schur blocks in, the front out) and every dependent step of the pivot chain
+// costs a shared-memory round trip instead of an L2 one.
+//
+// Shared leading dimension: lds = 2 (mod 4), which makes the DMMA B-fragment loads (4 rows
+// x 2 adjacent complex per quarter warp) bank-conflict free.
+__host__ __device__ __forceinline__ int smem_ld(int s) { return s + ((2 - (s & 3)) & 3); }
+
+struct PivotSmem {
+    int piv[TW];
+    int src[TW];
+    int sing;
+    int swapped;
+};
+
+// In-place Gauss-Jordan inversion of the n x n block at T (leading dimension ldt, shared
+// memory) with partial pivoting restricted to the block; same arithmetic and thread mapping
+// as invert_tile.  Before the update of step p every thread holds what other warps are about
+// to overwrite (its column of the normalised pivot row, of the old row p, and the old
+// T[p][p]) in registers, so a step costs two barriers and no staging buffer.  On return T
+// holds the inverse (row exchanges undone).
+template <int NT>
+__device__ __forceinline__ void invert_tile_inplace(cd* T, int ldt, int n, int tid, PivotSmem& ps) {
+    const int lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = NT / 32;
+    const int jl = min(lane, n - 1);
+    for (int p = 0; p < n; ++p) {
+        const unsigned key = pivot_search(T, ldt, n, p, lane);
+        const bool ok = (key >> 5) != 0u;
+        const int r = ok ? 31 - (int)(key & 31u) : p;
+        if (tid == 0) {
+            ps.piv[p] = r;
+            if (!ok) ps.sing = 1;
+            if (r != p) ps.swapped = 1;
+        }
+        const cd d = ok ? pivot_reciprocal(T[r * ldt + p], key) : make_double2(1.0, 0.0);
+        const cd rb = (lane == p) ? d : cmul(T[r * ldt + jl], d);
+        const cd pr = T[p * ldt + jl];
+        const cd fpp = T[p * ldt + p];
+        __syncthreads();
+        for (int i = warp; i < n; i += NW) {
+            cd out = rb;
+            if (i != p) {
+                cd f = fpp, a = pr;
+                if (i != r) { f = T[i * ldt + p]; a = T[i * ldt + jl]; }
+                if (lane == p) a = make_double2(0.0, 0.0);
+                out.x = fma(-f.x, rb.x, a.x); out.x = fma(f.y, rb.y, out.x);
+                out.y = fma(-f.x, rb.y, a.y); out.y = fma(-f.y, rb.x, out.y);
+            }
+            __syncwarp();      // every lane has read T[i][p] before lane p overwrites it
+            if (lane < n) T[i * ldt + lane] = out;
+        }
+        __syncthreads();
+    }
+    if (ps.swapped) {      // uniform: last written before the final barrier of the loop
+        // A^-1 = B P: column j of the result is column src[j] of B
+        if (tid == 0) {
+            for (int j = 0; j < n; ++j) ps.src[j] = j;
+            for (int p = n - 1; p >= 0; --p) {
+                int r = ps.piv[p], t = ps.src[p];
+                ps.src[p] = ps.src[r];
+                ps.src[r] = t;
+            }
+        }
+        __syncthreads();
+        for (int i = warp; i < n; i += NW) {     // a row belongs to one warp
+            cd v = make_double2(0.0, 0.0);
+            if (lane < n) v = T[i * ldt + ps.src[lane]];
+            __syncwarp();
+            if (lane < n) T[i * ldt + lane] = v;
+        }
+        __syncthreads();
+        if (tid == 0) ps.swapped = 0;
+    }
+}
+
+// One CTA per (front of this launch group, system); dynamic shared memory holds the front
+// (s x lds complex).  `data` is [nsys, nnz] in front-entry order (ENT_ORDER) or the caller's
+// CSC order.
+template <bool ENT_ORDER, int NT>
+__global__ void __launch_bounds__(NT, (NT >= 256 ? 1 : 512 / NT))
+factor_smem_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd* Fall,
+                   const cd* __restrict__ data, int* status) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cd* Fs = reinterpret_cast<cd*>(smem_raw);
+    __shared__ PivotSmem ps;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = NT / 32;
+    const int b = blockIdx.x % nsys;
+    const FrontDesc fd = sd.fr[level_fronts[blockIdx.x / nsys]];
+    cd* Fsys = Fall + (int64_t)b * sd.front_slots;
+    cd* Fg = Fsys + fd.off;
+    const int s = fd.s, k = fd.k, ld = fd.ld;
+    const int lds = smem_ld(s);
+
+    if (tid == 0) { ps.sing = 0; ps.swapped = 0; }
+    {
+        const cd zero = make_double2(0.0, 0.0);
+        const int tot = s * lds;
+        for (int e = tid; e < tot; e += NT) Fs[e] = zero;
+    }
+    __syncthreads();
+    // A entries: every entry owns its slot.  ent_slot is in the global layout (i * ld + j).
+    {
+        const cd* db = data + (int64_t)b * sd.nnz;
+        const float inv_ld = 1.0f / (float)ld;
+        constexpr int MLP = 4;
+        for (int q0 = tid; q0 < fd.nent; q0 += MLP * NT) {
+            cd v[MLP];
+            int sl[MLP];
+#pragma unroll
+            for (int u = 0; u < MLP; ++u) {
+                const int q = q0 + u * NT;
+                if (q < fd.nent) {
+                    const int64_t gq = fd.entptr + q;
+                    sl[u] = __ldg(sd.ent_slot + gq);
+                    v[u] = ENT_ORDER ? db[gq] : db[__ldg(sd.ent_src + gq)];
+                } else {
+                    sl[u] = -1;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < MLP; ++u)
+                if (sl[u] >= 0) {
+                    const int i = __float2int_rz(((float)sl[u] + 0.5f) * inv_ld);
+                    Fs[sl[u] + i * (lds - ld)] = v[u];
+                }
+        }
+    }
+    __syncthreads();
+    // extend-add: the children's Schur blocks stream from HBM, the scatter-add hits shared
+    for (int ci = 0; ci < fd.nchild; ++ci) {
+        const FrontDesc fc = sd.fr[sd.children[fd.childptr + ci]];
+        const int* rel = sd.relmap + fc.reloff;
+        const int mc = fc.s - fc.k;
+        const cd* Fc = Fsys + fc.off + (int64_t)fc.k * fc.ld + fc.k;
+        const int tot = mc * mc;
+        const float inv_mc = 1.0f / (float)mc;
+        constexpr int MLP = 8;
+        for (int e0 = tid; e0 < tot; e0 += MLP * NT) {
+            cd v[MLP];
+            int dst[MLP];
+#pragma unroll
+            for (int q = 0; q < MLP; ++q) {
+                const int e = e0 + q * NT;
+                if (e < tot) {
+                    const int i = __float2int_rz(((float)e + 0.5f) * inv_mc), j = e - i * mc;
+                    v[q] = Fc[i * fc.ld + j];
+                    dst[q] = __ldg(rel + i) * lds + __ldg(rel + j);
+                } else {
+                    dst[q] = -1;
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < MLP; ++q)
+                if (dst[q] >= 0) {
+                    cd o = Fs[dst[q]];
+                    o.x += v[q].x; o.y += v[q].y;
+                    Fs[dst[q]] = o;
+                }
+        }
+        __syncthreads();
+    }
+
+    // left-looking block factorisation of the pivot tiles, all operands in shared memory
+    const int KT = (k + TW - 1) / TW;
+    for (int J = 0; J < KT; ++J) {
+        const int j0 = J * TW;
+        const int jw = min(TW, k - j0);
+        const int j1 = j0 + jw;
+        if (J > 0) {
+            const int nct = (s - j0 + 15) >> 4;
+            const int nrr = (jw + 15) >> 4;
+            const int nrc = (s - j1 + 31) >> 5;
+            const int ntiles = nct + nrr * nrc;
+            for (int tile = warp; tile < ntiles; tile += NW) {
+                int r, c, mr, nc;
+                if (tile < nct) {
+                    r = j0 + 16 * tile; c = j0; mr = min(16, s - r); nc = jw;
+                } else {
+                    int q = tile - nct;
+                    r = j0 + 16 * (q % nrr); c = j1 + 32 * (q / nrr);
+                    mr = min(16, j1 - r); nc = min(32, s - c);
+                }
+                Acc<2, 4> acc;
+                acc.zero();
+                warp_gemm<2, 4>(acc, Fs + r * lds, lds, mr, Fs + c, lds, nc, j0, lane);
+                store_tile<2, 4, true>(acc, Fs + r * lds + c, lds, mr, nc, lane);
+            }
+            __syncthreads();
+        }
+        invert_tile_inplace<NT>(Fs + j0 * lds + j0, lds, jw, tid, ps);
         const int nlt = (s - j1 + 15) >> 4;
         for (int tile = warp; tile < nlt; tile += NW) {
             int r = j1 + 16 * tile, mr = min(16, s - r);
             Acc<2, 4> acc;
             acc.zero();
-            warp_gemm<2, 4>(acc, F + (int64_t)r * ld + j0, ld, mr, &Dinv[0][0], TLD, jw, jw, lane);
-            store_tile<2, 4, false>(acc, F + (int64_t)r * ld + j0, ld, mr, jw, lane);
+            warp_gemm<2, 4>(acc, Fs + r * lds + j0, lds, mr, Fs + j0 * lds + j0, lds, jw, jw, lane);
+            store_tile<2, 4, false>(acc, Fs + r * lds + j0, lds, mr, jw, lane);
         }
         __syncthreads();
     }
-    // ---- Schur complement of the contribution rows/cols
     const int m = s - k;
     if (m > 0 && k > 0) {
         const int ntr = (m + 15) >> 4, ntc = (m + 31) >> 5;
@@ -406,11 +675,18 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
             int mr = min(16, s - r), nc = min(32, s - c);
             Acc<2, 4> acc;
             acc.zero();
-            warp_gemm<2, 4>(acc, F + (int64_t)r * ld, ld, mr, F + c, ld, nc, k, lane);
-            store_tile<2, 4, true>(acc, F + (int64_t)r * ld + c, ld, mr, nc, lane);
+            warp_gemm<2, 4>(acc, Fs + r * lds, lds, mr, Fs + c, lds, nc, k, lane);
+            store_tile<2, 4, true>(acc, Fs + r * lds + c, lds, mr, nc, lane);
         }
+        __syncthreads();
     }
-    if (tid == 0 && ts.sing && status) atomicOr(status + b, 1);
+    // the finished front leaves in one pass: warp per row, lanes along the row
+    for (int i = warp; i < s; i += NW) {
+        const cd* src = Fs + i * lds;
+        cd* dst = Fg + (int64_t)i * ld;
+        for (int j = lane; j < s; j += 32) dst[j] = src[j];
+    }
+    if (tid == 0 && ps.sing && status) atomicOr(status + b, 1);
 }
 
 // ------------------------------------------------------------------------ triangular solves
