@@ -93,6 +93,9 @@ struct Pattern {
         int nt;
     };
     std::vector<std::vector<FactorGroup>> fgroups;
+    // triangular solves: per level {#fronts above wsolve_max (CTA per front), order of the
+    // largest remaining front (one warp per system)}
+    std::vector<std::array<int, 2>> wsolve;
     // symbolic data on the device
     FrontDesc* d_fr = nullptr;
     int *d_rowidx_orig = nullptr, *d_children = nullptr, *d_relmap = nullptr, *d_ent_src = nullptr,
@@ -241,7 +244,8 @@ struct Tuning {
     int front_big = 128, front_mid = 64;
     int nt[3] = {256, 128, 64};
     // shared-memory-resident fronts: order bound and CTA width of each class, ascending
-    int smem_max = 112;
+    int smem_max = 64;
+    int wsolve_max = 160;   // fronts up to this order: triangular solves with one warp per system
     int sbound[5] = {32, 48, 64, 80, 112};
     int snt[5] = {64, 64, 128, 128, 256};
     Tuning() {
@@ -257,6 +261,7 @@ struct Tuning {
         for (int& v : nt)
             if (v != 64 && v != 128 && v != 256) v = 128;
         smem_max = geti("JPB_SMEM_MAX", smem_max);
+        wsolve_max = std::min(320, geti("JPB_WSOLVE_MAX", wsolve_max));
         if (smem_max > 112) smem_max = 112;
         sbound[4] = std::max(smem_max, 81);
         const char* names[5] = {"JPB_SNT0", "JPB_SNT1", "JPB_SNT2", "JPB_SNT3", "JPB_SNT4"};
@@ -286,22 +291,6 @@ const Tuning& tuning() {
 }
 #define FRONT_BIG (tuning().front_big)
 #define FRONT_MID (tuning().front_mid)
-
-template <class Launch>
-void for_each_class(jpb_state* st, Pattern& P, int l, int64_t mult, Launch&& launch) {
-    const int n = P.levelptr[l + 1] - P.levelptr[l];
-    const int nbig = P.cls[l][0], nmid = P.cls[l][1], nsmall = n - nbig - nmid;
-    const int* lf = P.d_levelfronts + P.levelptr[l];
-    const int cnt[3] = {nbig, nmid, nsmall};
-    const int off[3] = {0, nbig, nbig + nmid};
-    for (int c = 0; c < 3; ++c) {
-        if (!cnt[c]) continue;
-        int64_t grid = (int64_t)cnt[c] * mult;
-        if (grid > 0x7fffffff) throw InvalidArg("wave too large for one launch");
-        launch(c, lf + off[c], (unsigned)grid);
-        launch_check(st);
-    }
-}
 
 // K1: vals[b, q] = sum_k coef[b, k] * mats_f[k, q]  (front-entry order), mats read once per
 // slice of ASM_BCHUNK systems
@@ -344,28 +333,63 @@ void factor(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* F, const cd
 }
 
 // x(b, j) = A_b^-1 rhs(b, j)  (or A_b^-T)
+constexpr int WSOLVE_NW = 8;     // systems (warps) per CTA of the warp-per-system solve kernels
 void tri_solve(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool trans, VecView vv, int phase) {
     Span span(st, s, phase);
     const size_t smem = (size_t)P.max_s * sizeof(cd);
     const int64_t mult = (int64_t)vv.nsys * vv.nrhs;
-#define JPB_SOLVE(KERNEL, NT)                                                      \
-    if (trans) KERNEL<true, NT><<<grid, NT, smem, s>>>(P.sd, lf, F, vv);           \
-    else KERNEL<false, NT><<<grid, NT, smem, s>>>(P.sd, lf, F, vv);
-    for (int l = 0; l < P.S.nlevels; ++l)
-        for_each_class(st, P, l, mult, [&](int c, const int* lf, unsigned grid) {
+    const int64_t wgroups = (mult + WSOLVE_NW - 1) / WSOLVE_NW;
+    // fronts of a level are sorted largest first: the first wsolve[l][0] go to the CTA-per-front
+    // kernels (by size class), the rest to the warp-per-system kernels
+    auto level = [&](int l, bool fwd) {
+        const int n = P.levelptr[l + 1] - P.levelptr[l];
+        const int nabove = P.wsolve[l][0];
+        const int* lf = P.d_levelfronts + P.levelptr[l];
+        const int nbig = std::min(P.cls[l][0], nabove), nmid = std::min(P.cls[l][1], nabove - nbig);
+        const int cnt[3] = {nbig, nmid, nabove - nbig - nmid};
+        int off = 0;
+        for (int c = 0; c < 3; ++c) {
+            if (!cnt[c]) continue;
+            const int64_t grid64 = (int64_t)cnt[c] * mult;
+            if (grid64 > 0x7fffffff) throw InvalidArg("wave too large for one launch");
+            const unsigned grid = (unsigned)grid64;
+            const int* lfc = lf + off;
             const int nt = tuning().nt[c];
-            if (nt == 256) { JPB_SOLVE(fwd_level_kernel, 256) }
-            else if (nt == 128) { JPB_SOLVE(fwd_level_kernel, 128) }
-            else { JPB_SOLVE(fwd_level_kernel, 64) }
-        });
-    for (int l = P.S.nlevels - 1; l >= 0; --l)
-        for_each_class(st, P, l, mult, [&](int c, const int* lf, unsigned grid) {
-            const int nt = tuning().nt[c];
-            if (nt == 256) { JPB_SOLVE(bwd_level_kernel, 256) }
-            else if (nt == 128) { JPB_SOLVE(bwd_level_kernel, 128) }
-            else { JPB_SOLVE(bwd_level_kernel, 64) }
-        });
+#define JPB_SOLVE(KERNEL, NT)                                                       \
+    if (trans) KERNEL<true, NT><<<grid, NT, smem, s>>>(P.sd, lfc, F, vv);           \
+    else KERNEL<false, NT><<<grid, NT, smem, s>>>(P.sd, lfc, F, vv);
+            if (fwd) {
+                if (nt == 256) { JPB_SOLVE(fwd_level_kernel, 256) }
+                else if (nt == 128) { JPB_SOLVE(fwd_level_kernel, 128) }
+                else { JPB_SOLVE(fwd_level_kernel, 64) }
+            } else {
+                if (nt == 256) { JPB_SOLVE(bwd_level_kernel, 256) }
+                else if (nt == 128) { JPB_SOLVE(bwd_level_kernel, 128) }
+                else { JPB_SOLVE(bwd_level_kernel, 64) }
+            }
 #undef JPB_SOLVE
+            launch_check(st);
+            off += cnt[c];
+        }
+        if (n > nabove) {
+            const int64_t grid64 = (int64_t)(n - nabove) * wgroups;
+            if (grid64 > 0x7fffffff) throw InvalidArg("wave too large for one launch");
+            const unsigned grid = (unsigned)grid64;
+            const int vstride = (P.wsolve[l][1] + 1) & ~1;
+            const size_t wsmem = (size_t)WSOLVE_NW * (vstride + TW) * sizeof(cd);
+            const int* lfw = lf + nabove;
+            if (fwd) {
+                if (trans) fwd_warp_kernel<true, WSOLVE_NW><<<grid, WSOLVE_NW * 32, wsmem, s>>>(P.sd, lfw, F, vv, vstride);
+                else fwd_warp_kernel<false, WSOLVE_NW><<<grid, WSOLVE_NW * 32, wsmem, s>>>(P.sd, lfw, F, vv, vstride);
+            } else {
+                if (trans) bwd_warp_kernel<true, WSOLVE_NW><<<grid, WSOLVE_NW * 32, wsmem, s>>>(P.sd, lfw, F, vv, vstride);
+                else bwd_warp_kernel<false, WSOLVE_NW><<<grid, WSOLVE_NW * 32, wsmem, s>>>(P.sd, lfw, F, vv, vstride);
+            }
+            launch_check(st);
+        }
+    };
+    for (int l = 0; l < P.S.nlevels; ++l) level(l, true);
+    for (int l = P.S.nlevels - 1; l >= 0; --l) level(l, false);
 }
 
 // y(b,j) = [rhs(b,j) -] op(A_b) x(b,j)
@@ -700,6 +724,16 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
             else if (sz > FRONT_MID) ++nmid;
         }
         P->cls[l] = {nbig, nmid};
+    }
+    P->wsolve.resize(S.nlevels);
+    for (int l = 0; l < S.nlevels; ++l) {
+        int nabove = 0, smax = 0;
+        for (int q = S.levelptr[l]; q < S.levelptr[l + 1]; ++q) {
+            const int sz = S.f_s[S.levelfronts[q]];
+            if (sz > tuning().wsolve_max) ++nabove;
+            else smax = std::max(smax, sz);
+        }
+        P->wsolve[l] = {nabove, smax};
     }
     // factor launch groups: fronts of a level are sorted largest first
     P->fgroups.assign(S.nlevels, {});

@@ -691,6 +691,51 @@ factor_smem_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd
 
 // ------------------------------------------------------------------------ triangular solves
 
+// transposing warp reductions (see K3w below for their use)
+__device__ __forceinline__ int row8(int lane) {
+    return ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+}
+__device__ __forceinline__ cd shfl_xor_cd(cd v, int m) {
+    return make_double2(__shfl_xor_sync(0xffffffffu, v.x, m), __shfl_xor_sync(0xffffffffu, v.y, m));
+}
+// Generalisation to lane groups of CW = 2^LB lanes (LB = 3, 4, 5): the 32 / CW groups of a
+// warp reduce independently; within a group the three upper lane bits select which of the 8
+// values a lane ends up with (sel8g) and the remaining LB - 3 bits are summed plainly.
+template <int LB>
+__device__ __forceinline__ int sel8g(int lane) {
+    return ((lane >> (LB - 1)) & 1) * 4 + ((lane >> (LB - 2)) & 1) * 2 + ((lane >> (LB - 3)) & 1);
+}
+template <int LB>
+__device__ __forceinline__ cd reduce8g(const cd (&p)[8], int lane) {
+    cd q[4], r[2];
+    const bool b4 = lane & (1 << (LB - 1)), b3 = lane & (1 << (LB - 2)), b2 = lane & (1 << (LB - 3));
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const cd send = b4 ? p[i] : p[i + 4], keep = b4 ? p[i + 4] : p[i];
+        const cd got = shfl_xor_cd(send, 1 << (LB - 1));
+        q[i] = make_double2(keep.x + got.x, keep.y + got.y);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const cd send = b3 ? q[i] : q[i + 2], keep = b3 ? q[i + 2] : q[i];
+        const cd got = shfl_xor_cd(send, 1 << (LB - 2));
+        r[i] = make_double2(keep.x + got.x, keep.y + got.y);
+    }
+    cd t;
+    {
+        const cd send = b2 ? r[0] : r[1], keep = b2 ? r[1] : r[0];
+        const cd got = shfl_xor_cd(send, 1 << (LB - 3));
+        t = make_double2(keep.x + got.x, keep.y + got.y);
+    }
+#pragma unroll
+    for (int o = (1 << (LB - 3)) >> 1; o > 0; o >>= 1) {
+        const cd got = shfl_xor_cd(t, o);
+        t.x += got.x; t.y += got.y;
+    }
+    return t;
+}
+__device__ __forceinline__ cd reduce8(const cd (&p)[8], int lane) { return reduce8g<5>(p, lane); }
+
 // rhs / solution addressing: system b, right-hand side j
 struct VecView {
     const cd* rhs;      // rhs(b, j) = rhs + (j * rhs_sj + b * rhs_sb) * N
@@ -741,21 +786,19 @@ fwd_level_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __re
     for (int J = 0; J < KT; ++J) {
         const int j0 = J * TW, jw = min(TW, k - j0), j1 = j0 + jw;
         if (!TRANS) {
-            // v[i] -= Lt[i, J] . v_J  for rows below the tile: warp per row, lane per column
+            // v[i] -= Lt[i, J] . v_J  for rows below the tile: eight rows per warp trip, lane per
+            // column, one transposing reduction per eight rows
             const cd vj = lane < jw ? v[j0 + lane] : make_double2(0.0, 0.0);
-            for (int i = j1 + 4 * warp; i < s; i += 4 * NW) {
-                cd a[4];
+            const cd* col = F + j0 + min(lane, jw - 1);
+            for (int i0 = j1 + 8 * warp; i0 < s; i0 += 8 * NW) {
+                cd p[8];
 #pragma unroll
-                for (int q = 0; q < 4; ++q)
-                    a[q] = (lane < jw && i + q < s) ? F[(int64_t)(i + q) * ld + j0 + lane]
-                                                     : make_double2(0.0, 0.0);
+                for (int q = 0; q < 8; ++q) p[q] = col[(int64_t)min(i0 + q, s - 1) * ld];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) a[q] = warp_sum(cmul(a[q], vj));
-                if (lane == 0) {
-#pragma unroll
-                    for (int q = 0; q < 4; ++q)
-                        if (i + q < s) { v[i + q].x -= a[q].x; v[i + q].y -= a[q].y; }
-                }
+                for (int q = 0; q < 8; ++q) p[q] = cmul(p[q], vj);
+                const cd t = reduce8(p, lane);
+                const int i = i0 + row8(lane);
+                if ((lane & 3) == 0 && i < s) { v[i].x -= t.x; v[i].y -= t.y; }
             }
             __syncthreads();
         } else {
@@ -851,6 +894,205 @@ bwd_level_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __re
         }
     }
     for (int i = tid; i < k; i += SOLVE_THREADS) x[rows[i]] = v[i];
+}
+
+// ------------------------------------------- triangular solves, one warp per system (K3w)
+// Small and mid-size fronts hold only a few KB of factor data each, so a CTA per (front,
+// system) spends its life fetching descriptors and index lists.  Here a CTA takes one front
+// for NW systems, one WARP per system: descriptors, row lists and extend-add maps are
+// fetched once per CTA (L1 serves the other warps), the front-local vector of a system lives
+// in that warp's slice of shared memory, and every synchronisation is a __syncwarp.
+//
+// reduce8: every lane holds 8 partial sums (rows 0..7 of a block); on return the lanes with
+// (lane & 3) == 0 hold the total of row row8(lane).  A transposing butterfly: 36 32-bit
+// shuffles per 8 rows instead of 160 for eight plain warp reductions.
+// v[i] -= Lt[i, J] . v_J for the rows i in [j1, s) of a pivot tile of width jw <= 2^LB: a warp
+// load covers 32 / CW rows x CW columns (CW = 2^LB), eight loads are in flight per lane, so a
+// narrow strip (jw <= 8: 32 rows) is one memory round trip.  v in shared memory.
+template <int LB>
+__device__ __forceinline__ void strip_fwd(const cd* F, int ld, int s, int j0, int jw, int j1, cd* v,
+                                          int lane) {
+    constexpr int CW = 1 << LB, RPL = 32 / CW;
+    const int c = lane & (CW - 1), ro = lane >> LB;
+    const cd zero = make_double2(0.0, 0.0);
+    const cd vj = c < jw ? v[j0 + c] : zero;
+    const cd* col = F + j0 + min(c, jw - 1);
+    for (int i0 = j1; i0 < s; i0 += 8 * RPL) {
+        cd p[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) p[q] = col[(int64_t)min(i0 + q * RPL + ro, s - 1) * ld];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) p[q] = cmul(p[q], vj);
+        const cd t = reduce8g<LB>(p, lane);
+        const int i = i0 + sel8g<LB>(lane) * RPL + ro;
+        if ((lane & ((CW >> 3) - 1)) == 0 && i < s) { v[i].x -= t.x; v[i].y -= t.y; }
+    }
+}
+// v[j0+c] -= sum_{i >= j1} Lt[i, j0+c] v[i]  (the transposed use of the same strip)
+template <int LB>
+__device__ __forceinline__ void strip_bwd_t(const cd* F, int ld, int s, int j0, int jw, int j1, cd* v,
+                                            int lane) {
+    constexpr int CW = 1 << LB, RPL = 32 / CW;
+    const int c = lane & (CW - 1), ro = lane >> LB;
+    cd acc = make_double2(0.0, 0.0);
+    const cd* col = F + j0 + min(c, jw - 1);
+    for (int i0 = j1; i0 < s; i0 += 8 * RPL) {
+        cd a[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) a[q] = col[(int64_t)min(i0 + q * RPL + ro, s - 1) * ld];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int i = i0 + q * RPL + ro;
+            if (i < s) cfma(acc, a[q], v[i]);
+        }
+    }
+#pragma unroll
+    for (int o = CW; o < 32; o <<= 1) {
+        const cd got = shfl_xor_cd(acc, o);
+        acc.x += got.x; acc.y += got.y;
+    }
+    __syncwarp();
+    if (lane < jw) { v[j0 + lane].x -= acc.x; v[j0 + lane].y -= acc.y; }
+}
+
+// per-warp shared slice: [vstride] front-local vector followed by [TW] scratch
+template <bool TRANS, int NW>
+__global__ void __launch_bounds__(NW * 32)
+fwd_warp_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __restrict__ Fall,
+                VecView vv, int vstride) {
+    extern __shared__ cd vsm[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nvec = vv.nsys * vv.nrhs;
+    const int groups = (nvec + NW - 1) / NW;
+    const int vec = (blockIdx.x % groups) * NW + warp;
+    if (vec >= nvec) return;          // no block-wide barrier below
+    const int b = vec % vv.nsys, jr = vec / vv.nsys;
+    const FrontDesc fd = sd.fr[level_fronts[blockIdx.x / groups]];
+    const cd* F = Fall + (int64_t)b * sd.front_slots + fd.off;
+    cd* V = vv.V + (int64_t)vec * sd.vec_slots;
+    const cd* rhs = vv.rhs + ((int64_t)jr * vv.rhs_sj + (int64_t)b * vv.rhs_sb) * sd.N;
+    const int s = fd.s, k = fd.k, ld = fd.ld;
+    const int* rows = sd.rowidx_orig + fd.rowptr;
+    cd* v = vsm + warp * (vstride + TW);
+    const cd zero = make_double2(0.0, 0.0);
+
+    for (int i = lane; i < s; i += 32) v[i] = i < k ? rhs[__ldg(rows + i)] : zero;
+    __syncwarp();
+    for (int ci = 0; ci < fd.nchild; ++ci) {
+        const FrontDesc fc = sd.fr[sd.children[fd.childptr + ci]];
+        const int* rel = sd.relmap + fc.reloff;
+        const int mc = fc.s - fc.k;
+        const cd* Vc = V + fc.voff + fc.k;
+        for (int i = lane; i < mc; i += 32) {
+            const cd a = Vc[i];
+            cd* p = v + __ldg(rel + i);
+            p->x += a.x;
+            p->y += a.y;
+        }
+        __syncwarp();
+    }
+    const int KT = (k + TW - 1) / TW;
+    for (int J = 0; J < KT; ++J) {
+        const int j0 = J * TW, jw = min(TW, k - j0), j1 = j0 + jw;
+        if (!TRANS) {
+            if (jw <= 8) strip_fwd<3>(F, ld, s, j0, jw, j1, v, lane);
+            else if (jw <= 16) strip_fwd<4>(F, ld, s, j0, jw, j1, v, lane);
+            else strip_fwd<5>(F, ld, s, j0, jw, j1, v, lane);
+            __syncwarp();
+        } else {
+            // z_J = D_J^-T v_J, then v[j] -= sum_p U[J_p, j] z_p right of the tile: lane = column
+            cd z = zero;
+            {
+                const cd* col = F + (int64_t)j0 * ld + j0 + min(lane, jw - 1);
+#pragma unroll 8
+                for (int p = 0; p < jw; ++p) cfma(z, col[(int64_t)p * ld], v[j0 + p]);
+            }
+            __syncwarp();
+            if (lane < jw) v[j0 + lane] = z;
+            __syncwarp();
+            for (int j = j1 + lane; j < s; j += 32) {
+                const cd* col = F + (int64_t)j0 * ld + j;
+                cd acc = zero;
+#pragma unroll 8
+                for (int p = 0; p < jw; ++p) cfma(acc, col[(int64_t)p * ld], v[j0 + p]);
+                v[j].x -= acc.x;
+                v[j].y -= acc.y;
+            }
+            __syncwarp();
+        }
+    }
+    cd* Vf = V + fd.voff;
+    for (int i = lane; i < s; i += 32) Vf[i] = v[i];
+}
+
+template <bool TRANS, int NW>
+__global__ void __launch_bounds__(NW * 32)
+bwd_warp_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __restrict__ Fall,
+                VecView vv, int vstride) {
+    extern __shared__ cd vsm[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nvec = vv.nsys * vv.nrhs;
+    const int groups = (nvec + NW - 1) / NW;
+    const int vec = (blockIdx.x % groups) * NW + warp;
+    if (vec >= nvec) return;
+    const int b = vec % vv.nsys;
+    const FrontDesc fd = sd.fr[level_fronts[blockIdx.x / groups]];
+    const cd* F = Fall + (int64_t)b * sd.front_slots + fd.off;
+    const cd* Vf = vv.V + (int64_t)vec * sd.vec_slots + fd.voff;
+    cd* x = vv.x + (int64_t)vec * sd.N;
+    const int s = fd.s, k = fd.k, ld = fd.ld;
+    const int* rows = sd.rowidx_orig + fd.rowptr;
+    cd* v = vsm + warp * (vstride + TW);
+    cd* tbuf = v + vstride;
+    const cd zero = make_double2(0.0, 0.0);
+
+    for (int i = lane; i < s; i += 32) v[i] = i < k ? Vf[i] : x[__ldg(rows + i)];
+    __syncwarp();
+    const int KT = (k + TW - 1) / TW;
+    for (int J = KT - 1; J >= 0; --J) {
+        const int j0 = J * TW, jw = min(TW, k - j0), j1 = j0 + jw;
+        if (!TRANS) {
+            // t_p = v[j0+p] - U[J_p, j1:] . v[j1:], eight rows of U per trip, lanes along the row
+            for (int p0 = 0; p0 < jw; p0 += 8) {
+                cd acc[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) acc[q] = zero;
+                const cd* row0 = F + (int64_t)(j0 + p0) * ld;
+                for (int j = j1 + lane; j < s; j += 32) {
+                    const cd vj = v[j];
+                    cd a[8];
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) a[q] = row0[(int64_t)min(q, jw - 1 - p0) * ld + j];
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) cfma(acc[q], a[q], vj);
+                }
+                const cd t = reduce8(acc, lane);
+                const int p = p0 + row8(lane);
+                if ((lane & 3) == 0 && p < jw) tbuf[p] = make_double2(v[j0 + p].x - t.x, v[j0 + p].y - t.y);
+            }
+            __syncwarp();
+            // v_J = D_J^-1 t
+            const cd tl = lane < jw ? tbuf[lane] : zero;
+            const cd* col = F + (int64_t)j0 * ld + j0 + min(lane, jw - 1);
+            for (int q0 = 0; q0 < jw; q0 += 8) {
+                cd p[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) p[q] = col[(int64_t)min(q0 + q, jw - 1) * ld];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) p[q] = cmul(p[q], tl);
+                const cd t = reduce8(p, lane);
+                const int qq = q0 + row8(lane);
+                if ((lane & 3) == 0 && qq < jw) v[j0 + qq] = t;
+            }
+            __syncwarp();
+        } else {
+            if (jw <= 8) strip_bwd_t<3>(F, ld, s, j0, jw, j1, v, lane);
+            else if (jw <= 16) strip_bwd_t<4>(F, ld, s, j0, jw, j1, v, lane);
+            else strip_bwd_t<5>(F, ld, s, j0, jw, j1, v, lane);
+            __syncwarp();
+        }
+    }
+    for (int i = lane; i < k; i += 32) x[__ldg(rows + i)] = v[i];
 }
 
 // ------------------------------------------------------------------------ sparse products
