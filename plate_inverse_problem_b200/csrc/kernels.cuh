@@ -175,6 +175,19 @@ __device__ __forceinline__ void warp_gemm(Acc<MB, NB>& acc, const cd* A, int lda
     }
 }
 
+// Ask L1 for the 16 x (8 NB) tile at C ahead of the k-loop, so that the read-modify-write of
+// store_tile<SUB = true> does not wait a full L2 round trip after the last DMMA.
+template <int NB>
+__device__ __forceinline__ void prefetch_tile(const cd* C, int ldc, int mrows, int ncols, int lane) {
+    const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+        const int i = min(8 * m + g, mrows - 1);
+        const int j = min(t * (2 * NB), ncols - 1);        // one 128-byte line = 8 complex
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(C + (int64_t)i * ldc + j));
+    }
+}
+
 // SUB = false: C = P ; SUB = true: C -= P   (P = accumulated product)
 template <int MB, int NB, bool SUB>
 __device__ __forceinline__ void store_tile(const Acc<MB, NB>& acc, cd* C, int ldc, int mrows,
@@ -409,6 +422,7 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
                 }
                 Acc<2, WN> acc;
                 acc.zero();
+                prefetch_tile<WN>(F + (int64_t)r * ld + c, ld, mr, nc, lane);
                 warp_gemm<2, WN>(acc, F + (int64_t)r * ld, ld, mr, F + c, ld, nc, j0, lane);
                 store_tile<2, WN, true>(acc, F + (int64_t)r * ld + c, ld, mr, nc, lane);
             }
@@ -454,6 +468,7 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
             int mr = min(16, s - r), nc = min(WC, s - c);
             Acc<2, WN> acc;
             acc.zero();
+            prefetch_tile<WN>(F + (int64_t)r * ld + c, ld, mr, nc, lane);
             warp_gemm<2, WN>(acc, F + (int64_t)r * ld, ld, mr, F + c, ld, nc, k, lane);
             store_tile<2, WN, true>(acc, F + (int64_t)r * ld + c, ld, mr, nc, lane);
         }
