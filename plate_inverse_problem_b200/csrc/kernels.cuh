@@ -280,17 +280,29 @@ __device__ __forceinline__ int invert_tile(TileSmem& ts, int n, int tid) {
         const cd d = ok ? pivot_reciprocal(Dc[r * TLD + p], key) : make_double2(1.0, 0.0);
         if (lane < n) {
             const cd rb = (lane == p) ? d : cmul(Dc[r * TLD + lane], d);
-            for (int i = warp; i < n; i += NW) {
-                cd out = rb;
-                if (i != p) {
+            // four rows per trip: the eight shared loads go out together and the four FMA
+            // chains interleave (a warp's progress here is bounded by dependent-issue latency)
+            const cd* Dl = Dc + lane;
+            const cd* Dp = Dc + p;
+            for (int i0 = warp; i0 < n; i0 += 4 * NW) {
+                cd f[4], a[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int i = min(i0 + u * NW, n - 1);
                     const int oi = (i == r) ? p : i;     // rows p and r trade places
-                    const cd f = Dc[oi * TLD + p];
-                    out = Dc[oi * TLD + lane];
-                    if (lane == p) out = make_double2(0.0, 0.0);
-                    out.x = fma(-f.x, rb.x, out.x); out.x = fma(f.y, rb.y, out.x);
-                    out.y = fma(-f.x, rb.y, out.y); out.y = fma(-f.y, rb.x, out.y);
+                    f[u] = Dp[oi * TLD];
+                    a[u] = Dl[oi * TLD];
                 }
-                Dn[i * TLD + lane] = out;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int i = i0 + u * NW;
+                    cd out = a[u];
+                    if (lane == p) out = make_double2(0.0, 0.0);
+                    out.x = fma(-f[u].x, rb.x, out.x); out.x = fma(f[u].y, rb.y, out.x);
+                    out.y = fma(-f[u].x, rb.y, out.y); out.y = fma(-f[u].y, rb.x, out.y);
+                    if (i == p) out = rb;
+                    if (i < n) Dn[i * TLD + lane] = out;
+                }
             }
         }
         __syncthreads();
@@ -520,17 +532,26 @@ __device__ __forceinline__ void invert_tile_inplace(cd* T, int ldt, int n, int t
         const cd pr = T[p * ldt + jl];
         const cd fpp = T[p * ldt + p];
         __syncthreads();
-        for (int i = warp; i < n; i += NW) {
-            cd out = rb;
-            if (i != p) {
-                cd f = fpp, a = pr;
-                if (i != r) { f = T[i * ldt + p]; a = T[i * ldt + jl]; }
-                if (lane == p) a = make_double2(0.0, 0.0);
-                out.x = fma(-f.x, rb.x, a.x); out.x = fma(f.y, rb.y, out.x);
-                out.y = fma(-f.x, rb.y, a.y); out.y = fma(-f.y, rb.x, out.y);
+        for (int i0 = warp; i0 < n; i0 += 4 * NW) {      // four rows per trip (see invert_tile)
+            cd f[4], a[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = min(i0 + u * NW, n - 1);
+                f[u] = T[i * ldt + p];
+                a[u] = T[i * ldt + jl];
+                if (i == r) { f[u] = fpp; a[u] = pr; }
             }
             __syncwarp();      // every lane has read T[i][p] before lane p overwrites it
-            if (lane < n) T[i * ldt + lane] = out;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * NW;
+                cd out = a[u];
+                if (lane == p) out = make_double2(0.0, 0.0);
+                out.x = fma(-f[u].x, rb.x, out.x); out.x = fma(f[u].y, rb.y, out.x);
+                out.y = fma(-f[u].x, rb.y, out.y); out.y = fma(-f[u].y, rb.x, out.y);
+                if (i == p) out = rb;
+                if (i < n && lane < n) T[i * ldt + lane] = out;
+            }
         }
         __syncthreads();
     }
