@@ -35,6 +35,9 @@ PARAMS = np.array([130e9, 9e9, 5e9, 0.3, 0.01])
 ANGLES = (0, 45, -45, 90)
 FREQS_PER_GPU = {"cfg1": 400, "cfg0": 400, "small": 64, "cfg4": 96, "cfg5": 160, "40k": 256}
 METRIC = "freq-point forward+adjoint+grad evals/s"
+# DRAM bytes moved by the factor launches of one wave, from the committed ncu launch list
+# (profiles/r1h_launches_cfg1_F400.csv: 60.2 + 5.1 GB read, 57.8 + 11.3 GB written)
+FACTOR_DRAM_BYTES = {("cfg1", 400): 134.4e9}
 
 
 def make_inputs(workload):
@@ -305,8 +308,12 @@ def run_ours(args):
             gpu_launches=int(tm["launches"] * args.steps),
             clocks=clocks.summary(),
             roofline=dict(bound="tensor", achieved=fac_tf, peak=float(peak[0]), unit="TFLOP/s",
-                          frac=fac_tf / float(peak[0]), traffic=None,
-                          kernel="factor_level_kernel<fused> (all levels of one wave)",
+                          frac=fac_tf / float(peak[0]),
+                          traffic=FACTOR_DRAM_BYTES.get((wl, nloc)),
+                          traffic_note="dram__bytes_read+write summed over the factor launches of one "
+                                       "wave (ncu launch list profiles/r1h_launches_cfg1_F400.csv)",
+                          kernel="numeric factorisation of one wave: factor_smem_kernel (fronts <= 64) + "
+                                 "factor_level_kernel (larger fronts), all levels",
                           note="FP64 DMMA (mma.sync m8n8k4) peak measured live by jpb_dmma_peak; "
                                "MEASURED_PEAKS.json holds no FP64 figure",
                           flops_per_system=info["flops"], systems_per_launch_group=nloc),

@@ -188,7 +188,11 @@ def _abd_and_jacobian(transform, p0, omega, with_jacobian):
     abd = flat(p0)
     if not with_jacobian:
         return abd, None
-    J = torch.autograd.functional.jacobian(lambda p: torch.view_as_real(flat(p)), p0)   # [18, 2, P]
+    fn = lambda p: torch.view_as_real(flat(p))
+    try:        # one vmapped backward pass instead of 36 (same numbers, ~7x less host time)
+        J = torch.autograd.functional.jacobian(fn, p0, vectorize=True)   # [18, 2, P]
+    except RuntimeError:     # a user transform with ops vmap cannot batch
+        J = torch.autograd.functional.jacobian(fn, p0)
     return abd, torch.complex(J[:, 0, :], J[:, 1, :])
 
 
