@@ -79,9 +79,11 @@ def union_pattern_and_align(mats, N: int, index_dtype=np.int64):
         return m.row.astype(np.int64) + np.int64(N) * m.col.astype(np.int64)
 
     mats = [m.tocoo() for m in mats]
-    pattern = np.array([], dtype=np.int64)
-    for m in mats:
-        pattern = np.union1d(pattern, unwind(m))
+    # the reference folds np.union1d over the 26 key arrays (`Problem.py:320-326`); the sorted
+    # set of unique keys it ends with is what one sort + adjacent-difference mask gives
+    # (numpy 2.3's hash-based unique degrades badly on these structured keys at N ~ 1e5)
+    pattern = np.sort(np.concatenate([unwind(m) for m in mats]))
+    pattern = pattern[np.concatenate(([True], pattern[1:] != pattern[:-1]))] if pattern.size else pattern
     rows = pattern % N
     cols = pattern // N
     nz_idx = np.vstack((rows, cols)).T.astype(index_dtype)
