@@ -99,7 +99,7 @@ struct Pattern {
     // symbolic data on the device
     FrontDesc* d_fr = nullptr;
     int *d_rowidx_orig = nullptr, *d_children = nullptr, *d_relmap = nullptr, *d_ent_src = nullptr,
-        *d_ent_slot = nullptr, *d_levelfronts = nullptr;
+        *d_ent_slot = nullptr, *d_levelfronts = nullptr, *d_cbinv = nullptr;
     // sparse views: CSC (as given) and CSR (rebuilt); *_pos_ent map into front-entry order
     int *d_csc_ptr = nullptr, *d_csc_row = nullptr, *d_csc_col = nullptr, *d_csc_pos_ent = nullptr;
     int *d_csr_ptr = nullptr, *d_csr_col = nullptr, *d_csr_pos = nullptr, *d_csr_pos_ent = nullptr;
@@ -111,7 +111,7 @@ struct Pattern {
 
     ~Pattern() {
         void* ptrs[] = {d_fr, d_rowidx_orig, d_children, d_relmap, d_ent_src, d_ent_slot,
-                        d_levelfronts, d_csc_ptr, d_csc_row, d_csc_col, d_csc_pos_ent, d_csr_ptr,
+                        d_levelfronts, d_cbinv, d_csc_ptr, d_csc_row, d_csc_col, d_csc_pos_ent, d_csr_ptr,
                         d_csr_col, d_csr_pos, d_csr_pos_ent, d_mats, d_mats_f, d_rhs_vec, d_Q};
         for (void* p : ptrs)
             if (p) cudaFree(p);
@@ -710,7 +710,8 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
         d.nchild = S.f_childptr[f + 1] - S.f_childptr[f];
         d.reloff = (int)std::max<int64_t>(S.f_reloff[f], 0);
         d.parent = S.f_parent[f];
-        d.pad0 = d.pad1 = 0;
+        d.npan = 0;
+        d.invoff = 0;
     }
     if (!S.relmap.empty() && (int64_t)S.relmap.size() > INT32_MAX) throw InvalidArg("add_mat: pattern too large");
     P->levelptr = S.levelptr;
@@ -765,6 +766,30 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
             }
         }
     }
+    // inverse extend-add maps (parent contribution row -> child contribution row) and the
+    // number of child rows that land on parent pivots; the factor kernel for large fronts
+    // gathers the children's Schur blocks with them while it writes its own (no zero fill,
+    // no scatter read-modify-write of the contribution block)
+    std::vector<int> cbinv;
+    for (int c = 0; c < S.nfronts; ++c) {
+        const int p = S.f_parent[c];
+        if (p < 0) continue;
+        const int kp = S.f_k[p], mp = S.f_s[p] - kp, mc = S.f_s[c] - S.f_k[c];
+        fr[c].invoff = (int)cbinv.size();
+        cbinv.resize(cbinv.size() + mp, -1);
+        int npan = 0;
+        for (int i = 0; i < mc; ++i) {
+            const int r = S.relmap[S.f_reloff[c] + i];
+            if (r < kp) {
+                if (npan != i) throw InvalidArg("add_mat: extend-add map is not pivot-rows-first");
+                ++npan;
+            }
+            else cbinv[fr[c].invoff + (r - kp)] = i;
+        }
+        fr[c].npan = npan;
+    }
+    if (cbinv.size() > (size_t)INT32_MAX) throw InvalidArg("add_mat: pattern too large");
+    P->d_cbinv = upload(cbinv);
     P->d_fr = upload(fr);
     P->d_rowidx_orig = upload(S.rowidx_orig);
     P->d_children = upload(S.children);
@@ -780,7 +805,7 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
     P->d_csr_col = upload(csr_col);
     P->d_csr_pos = upload(csr_pos);
     P->d_csr_pos_ent = upload(csr_pos_ent);
-    P->sd = SymDev{P->d_fr, P->d_rowidx_orig, P->d_children, P->d_relmap, P->d_ent_src, P->d_ent_slot,
+    P->sd = SymDev{P->d_fr, P->d_rowidx_orig, P->d_children, P->d_relmap, P->d_ent_src, P->d_ent_slot, P->d_cbinv,
                    S.front_slots, S.vec_slots, S.nnz, S.N};
     // the dynamic shared memory of the solve kernels holds one front-local vector
     size_t smem = (size_t)S.max_s * sizeof(cd);

@@ -27,7 +27,8 @@ struct FrontDesc {
     int childptr, nchild;
     int reloff;       // this front's CB rows -> parent-local rows (into relmap)
     int parent;
-    int pad0, pad1;
+    int npan;         // as a child: how many of its contribution rows land on pivots of the parent
+    int invoff;       // as a child: first slot of its inverse map in cbinv
 };
 
 struct SymDev {
@@ -37,6 +38,9 @@ struct SymDev {
     const int* relmap;
     const int* ent_src;
     const int* ent_slot;
+    // for child c and contribution row q of its parent (q = parent row - k_parent):
+    // cbinv[invoff(c) + q] = contribution row of c that lands there, or -1
+    const int* cbinv;
     int64_t front_slots;
     int64_t vec_slots;
     int64_t nnz;
@@ -217,6 +221,62 @@ __device__ __forceinline__ void store_tile(const Acc<MB, NB>& acc, cd* C, int ld
     }
 }
 
+// Epilogue of a contribution-block tile: C(i, j) = sum_children child(inv_c[i], inv_c[j]) - P(i, j)
+// with P the accumulated product Lt * U.  (rc, cc) is the tile's position inside the block;
+// every element of the block is written exactly once and never read here.
+template <int MB, int NB>
+__device__ __forceinline__ void store_tile_cb(const Acc<MB, NB>& acc, cd* C, int ldc, int mrows, int ncols,
+                                              int rc, int cc, const SymDev& sd, const FrontDesc& fd,
+                                              const cd* Fsys, int lane) {
+    const int g = lane >> 2, t = lane & 3;
+    cd val[MB][NB][2];
+#pragma unroll
+    for (int m = 0; m < MB; ++m)
+#pragma unroll
+        for (int n = 0; n < NB; ++n)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) val[m][n][e] = make_double2(-acc.re[m][n][e], -acc.im[m][n][e]);
+    for (int ci = 0; ci < fd.nchild; ++ci) {
+        const FrontDesc fc = sd.fr[sd.children[fd.childptr + ci]];
+        const int* inv = sd.cbinv + fc.invoff;
+        const cd* Fc = Fsys + fc.off + (int64_t)fc.k * fc.ld + fc.k;
+        int ri[MB], cj[NB][2];
+#pragma unroll
+        for (int m = 0; m < MB; ++m) ri[m] = 8 * m + g < mrows ? __ldg(inv + rc + 8 * m + g) : -1;
+#pragma unroll
+        for (int n = 0; n < NB; ++n)
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+                cj[n][e] = 8 * n + 2 * t + e < ncols ? __ldg(inv + cc + 8 * n + 2 * t + e) : -1;
+#pragma unroll
+        for (int m = 0; m < MB; ++m) {
+            if (ri[m] < 0) continue;
+            const cd* row = Fc + (int64_t)ri[m] * fc.ld;
+#pragma unroll
+            for (int n = 0; n < NB; ++n)
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+                    if (cj[n][e] >= 0) {
+                        const cd a = row[cj[n][e]];
+                        val[m][n][e].x += a.x;
+                        val[m][n][e].y += a.y;
+                    }
+        }
+    }
+#pragma unroll
+    for (int m = 0; m < MB; ++m) {
+        const int i = 8 * m + g;
+        if (i >= mrows) continue;
+#pragma unroll
+        for (int n = 0; n < NB; ++n)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int j = 8 * n + 2 * t + e;
+                if (j < ncols) C[(int64_t)i * ldc + j] = val[m][n][e];
+            }
+    }
+}
+
 // --------------------------------------------------------------- pivot-tile inversion
 constexpr int TW = 32;        // pivot tile width
 constexpr int TLD = TW + 1;   // shared-memory leading dimension
@@ -359,10 +419,16 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
 
     if (tid == 0) { ts.sing = 0; ts.swapped = 0; }
     // ---- zero, then A entries (every entry owns its slot), then the children one by one
+    // Only the pivot rows and pivot columns are assembled by zero + scatter; the contribution
+    // block (rows and columns >= k) is written exactly once, by the Schur phase, which gathers
+    // the children's blocks through the inverse maps while it stores (store_tile_cb).
     {
         const cd zero = make_double2(0.0, 0.0);
-        const int tot = s * ld;
-        for (int e = tid; e < tot; e += FACTOR_THREADS) F[e] = zero;
+        for (int i = warp; i < s; i += NW) {
+            cd* row = F + (int64_t)i * ld;
+            const int lim = i < k ? s : k;
+            for (int j = lane; j < lim; j += 32) row[j] = zero;
+        }
     }
     __syncthreads();
     // A entries: ENT_ORDER = true : data[b, q] already in front-entry order (written by the
@@ -378,12 +444,12 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
     for (int ci = 0; ci < fd.nchild; ++ci) {
         const FrontDesc fc = sd.fr[sd.children[fd.childptr + ci]];
         const int* rel = sd.relmap + fc.reloff;
-        const int mc = fc.s - fc.k;
+        const int mc = fc.s - fc.k, pc = fc.npan;
         const cd* Fc = Fsys + fc.off + (int64_t)fc.k * fc.ld + fc.k;
-        // flattened (i, j) over all threads, eight independent elements in flight per
-        // thread: the child's block streams from HBM, the parent's slots sit in L2, and a
-        // dependent load->add->store chain per element would leave both idle.
-        const int tot = mc * mc;
+        // the part of the child's block that lands on pivot rows or pivot columns: its first pc
+        // rows in full, then the first pc columns of the other rows.  Flattened over all
+        // threads, eight independent elements in flight per thread.
+        const int top = pc * mc, tot = top + (mc - pc) * pc;
         constexpr int MLP = 8;
         for (int e0 = tid; e0 < tot; e0 += MLP * FACTOR_THREADS) {
             cd v[MLP];
@@ -392,7 +458,9 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
             for (int q = 0; q < MLP; ++q) {
                 const int e = e0 + q * FACTOR_THREADS;
                 if (e < tot) {
-                    const int i = e / mc, j = e - i * mc;
+                    int i, j;
+                    if (e < top) { i = e / mc; j = e - i * mc; }
+                    else { const int e2 = e - top; i = e2 / pc; j = e2 - i * pc; i += pc; }
                     v[q] = Fc[(int64_t)i * fc.ld + j];
                     p[q] = F + (int64_t)rel[i] * ld + rel[j];
                 } else {
@@ -471,18 +539,18 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
         }
         __syncthreads();
     }
-    // ---- Schur complement of the contribution rows/cols
+    // ---- contribution block: C = sum over children of their blocks (gathered) - Lt * U
     const int m = s - k;
-    if (m > 0 && k > 0) {
+    if (m > 0) {
         const int ntr = (m + 15) >> 4, ntc = (m + WC - 1) / WC;
         for (int tile = warp; tile < ntr * ntc; tile += NW) {
-            int r = k + 16 * (tile % ntr), c = k + WC * (tile / ntr);
-            int mr = min(16, s - r), nc = min(WC, s - c);
+            const int rc = 16 * (tile % ntr), cc = WC * (tile / ntr);      // within the block
+            const int r = k + rc, c = k + cc;
+            const int mr = min(16, s - r), nc = min(WC, s - c);
             Acc<2, WN> acc;
             acc.zero();
-            prefetch_tile<WN>(F + (int64_t)r * ld + c, ld, mr, nc, lane);
             warp_gemm<2, WN>(acc, F + (int64_t)r * ld, ld, mr, F + c, ld, nc, k, lane);
-            store_tile<2, WN, true>(acc, F + (int64_t)r * ld + c, ld, mr, nc, lane);
+            store_tile_cb<2, WN>(acc, F + (int64_t)r * ld + c, ld, mr, nc, rc, cc, sd, fd, Fsys, lane);
         }
     }
     if (tid == 0 && ts.sing && status) atomicOr(status + b, 1);
