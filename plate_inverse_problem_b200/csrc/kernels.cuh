@@ -313,6 +313,23 @@ __device__ __forceinline__ cd pivot_reciprocal(cd z, unsigned key) {
     return make_double2(zx * q, -zy * q);
 }
 
+// Column source map of the row exchanges: A^-1 = B P, i.e. column j of the result is column
+// src[j] of B, with src = the transpositions (p, piv[p]) applied to the identity from the last
+// pivot to the first.  Every warp derives it redundantly in registers (lane j ends up with
+// src[j]; three shuffles per pivot), so nobody waits on a serial loop of one thread.
+__device__ __forceinline__ int pivot_column_source(const int* piv, int n, int lane) {
+    const int mine = lane < n ? piv[lane] : lane;
+    int src = lane;
+    for (int p = n - 1; p >= 0; --p) {
+        const int r = __shfl_sync(0xffffffffu, mine, p);
+        const int vr = __shfl_sync(0xffffffffu, src, r);
+        const int vp = __shfl_sync(0xffffffffu, src, p);
+        if (lane == p) src = vr;
+        else if (lane == r) src = vp;
+    }
+    return src;
+}
+
 // Gauss-Jordan inversion of the n x n block in ts.D[0] with partial pivoting restricted to
 // the block (row exchanges only move rows inside the pivot tile, so the static front
 // structure is unaffected: D^-1 absorbs the permutation).  Double buffered: step p reads
@@ -370,17 +387,9 @@ __device__ __forceinline__ int invert_tile(TileSmem& ts, int n, int tid) {
     }
     // undo the row exchanges: A^-1 = B P  <=>  column j of the result is column src[j] of B
     if (ts.swapped) {      // uniform: last written before the final barrier of the loop
-        if (tid == 0) {
-            for (int j = 0; j < n; ++j) ts.src[j] = j;
-            for (int p = n - 1; p >= 0; --p) {
-                int r = ts.piv[p], t = ts.src[p];
-                ts.src[p] = ts.src[r];
-                ts.src[r] = t;
-            }
-        }
-        __syncthreads();
+        const int src = pivot_column_source(ts.piv, n, lane);
         if (lane < n)
-            for (int i = warp; i < n; i += NW) ts.D[cur ^ 1][i][lane] = ts.D[cur][i][ts.src[lane]];
+            for (int i = warp; i < n; i += NW) ts.D[cur ^ 1][i][lane] = ts.D[cur][i][src];
         __syncthreads();
         if (tid == 0) ts.swapped = 0;
         cur ^= 1;
@@ -625,18 +634,10 @@ __device__ __forceinline__ void invert_tile_inplace(cd* T, int ldt, int n, int t
     }
     if (ps.swapped) {      // uniform: last written before the final barrier of the loop
         // A^-1 = B P: column j of the result is column src[j] of B
-        if (tid == 0) {
-            for (int j = 0; j < n; ++j) ps.src[j] = j;
-            for (int p = n - 1; p >= 0; --p) {
-                int r = ps.piv[p], t = ps.src[p];
-                ps.src[p] = ps.src[r];
-                ps.src[r] = t;
-            }
-        }
-        __syncthreads();
+        const int src = pivot_column_source(ps.piv, n, lane);
         for (int i = warp; i < n; i += NW) {     // a row belongs to one warp
             cd v = make_double2(0.0, 0.0);
-            if (lane < n) v = T[i * ldt + ps.src[lane]];
+            if (lane < n) v = T[i * ldt + src];
             __syncwarp();
             if (lane < n) T[i * ldt + lane] = v;
         }
