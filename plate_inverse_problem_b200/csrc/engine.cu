@@ -246,8 +246,10 @@ struct Tuning {
     // shared-memory-resident fronts: order bound and CTA width of each class, ascending
     int smem_max = 64;
     int wsolve_max = 160;   // fronts up to this order: triangular solves with one warp per system
-    int sbound[5] = {32, 48, 64, 80, 112};
-    int snt[5] = {64, 64, 128, 128, 256};
+    // ... launch groups of `smem_step` consecutive orders (the group's largest front sizes the
+    // shared memory, so finer groups mean more resident CTAs for the smaller fronts);
+    // CTA width 64 up to order smem_nt64, 128 up to smem_nt128, 256 above
+    int smem_step = 4, smem_nt64 = 48, smem_nt128 = 80;
     Tuning() {
         auto geti = [](const char* name, int def) {
             const char* v = getenv(name);
@@ -263,12 +265,9 @@ struct Tuning {
         smem_max = geti("JPB_SMEM_MAX", smem_max);
         wsolve_max = std::min(320, geti("JPB_WSOLVE_MAX", wsolve_max));
         if (smem_max > 112) smem_max = 112;
-        sbound[4] = std::max(smem_max, 81);
-        const char* names[5] = {"JPB_SNT0", "JPB_SNT1", "JPB_SNT2", "JPB_SNT3", "JPB_SNT4"};
-        for (int c = 0; c < 5; ++c) {
-            snt[c] = geti(names[c], snt[c]);
-            if (snt[c] != 64 && snt[c] != 128 && snt[c] != 256) snt[c] = 128;
-        }
+        smem_step = std::max(1, geti("JPB_SMEM_STEP", smem_step));
+        smem_nt64 = geti("JPB_SMEM_NT64", smem_nt64);
+        smem_nt128 = geti("JPB_SMEM_NT128", smem_nt128);
     }
 };
 // symbolic options, overridable for tuning runs (JPB_LEAF, JPB_RELAX_SMALL, ...)
@@ -746,10 +745,8 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
                 nt = tn.nt[c];
                 return c;
             }
-            int c = 0;
-            while (c < 4 && sz > tn.sbound[c]) ++c;
-            nt = tn.snt[c];
-            return 3 + (4 - c);
+            nt = sz <= tn.smem_nt64 ? 64 : (sz <= tn.smem_nt128 ? 128 : 256);
+            return 3 + (sz + tn.smem_step - 1) / tn.smem_step;
         };
         for (int l = 0; l < S.nlevels; ++l) {
             int prev = -1;

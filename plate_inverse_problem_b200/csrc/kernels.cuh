@@ -179,6 +179,40 @@ __device__ __forceinline__ void warp_gemm(Acc<MB, NB>& acc, const cd* A, int lda
     }
 }
 
+// The same product with both operands in shared memory: at ~30 cycles of load latency the
+// next k-step's operands need no register double buffer, which frees 24 registers and lets
+// more of the small shared-memory-resident fronts be co-resident.
+template <int MB, int NB>
+__device__ __forceinline__ void warp_gemm_shared(Acc<MB, NB>& acc, const cd* A, int lda, int mrows,
+                                                 const cd* B, int ldb, int ncols, int K, int lane) {
+    const int g = lane >> 2, t = lane & 3;
+    int oa[MB], ob[NB];
+#pragma unroll
+    for (int m = 0; m < MB; ++m) oa[m] = min(8 * m + g, mrows - 1) * lda + t;
+#pragma unroll
+    for (int n = 0; n < NB; ++n) ob[n] = t * ldb + min(8 * n + g, ncols - 1);
+    const int nfull = K >> 2;
+#pragma unroll 1
+    for (int it = 0; it < nfull; ++it) {
+        cd a[MB], b[NB];
+#pragma unroll
+        for (int m = 0; m < MB; ++m) a[m] = A[oa[m] + 4 * it];
+#pragma unroll
+        for (int n = 0; n < NB; ++n) b[n] = B[ob[n] + 4 * it * ldb];
+        warp_mma_step<MB, NB>(acc, a, b);
+    }
+    const int rem = K & 3;
+    if (rem) {
+        cd a[MB], b[NB];
+        const cd zero = make_double2(0.0, 0.0);
+#pragma unroll
+        for (int m = 0; m < MB; ++m) a[m] = t < rem ? A[oa[m] + 4 * nfull] : zero;
+#pragma unroll
+        for (int n = 0; n < NB; ++n) b[n] = t < rem ? B[ob[n] + 4 * nfull * ldb] : zero;
+        warp_mma_step<MB, NB>(acc, a, b);
+    }
+}
+
 // Ask L1 for the 16 x (8 NB) tile at C ahead of the k-loop, so that the read-modify-write of
 // store_tile<SUB = true> does not wait a full L2 round trip after the last DMMA.
 template <int NB>
@@ -649,8 +683,11 @@ __device__ __forceinline__ void invert_tile_inplace(cd* T, int ldt, int n, int t
 // One CTA per (front of this launch group, system); dynamic shared memory holds the front
 // (s x lds complex).  `data` is [nsys, nnz] in front-entry order (ENT_ORDER) or the caller's
 // CSC order.
+#ifndef JPB_SMEM_OCC
+#define JPB_SMEM_OCC 512
+#endif
 template <bool ENT_ORDER, int NT>
-__global__ void __launch_bounds__(NT, (NT >= 256 ? 1 : 512 / NT))
+__global__ void __launch_bounds__(NT, (NT >= 256 ? 1 : JPB_SMEM_OCC / NT))
 factor_smem_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd* Fall,
                    const cd* __restrict__ data, int* status) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -756,7 +793,7 @@ factor_smem_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd
                 }
                 Acc<2, 4> acc;
                 acc.zero();
-                warp_gemm<2, 4>(acc, Fs + r * lds, lds, mr, Fs + c, lds, nc, j0, lane);
+                warp_gemm_shared<2, 4>(acc, Fs + r * lds, lds, mr, Fs + c, lds, nc, j0, lane);
                 store_tile<2, 4, true>(acc, Fs + r * lds + c, lds, mr, nc, lane);
             }
             __syncthreads();
@@ -767,7 +804,7 @@ factor_smem_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd
             int r = j1 + 16 * tile, mr = min(16, s - r);
             Acc<2, 4> acc;
             acc.zero();
-            warp_gemm<2, 4>(acc, Fs + r * lds + j0, lds, mr, Fs + j0 * lds + j0, lds, jw, jw, lane);
+            warp_gemm_shared<2, 4>(acc, Fs + r * lds + j0, lds, mr, Fs + j0 * lds + j0, lds, jw, jw, lane);
             store_tile<2, 4, false>(acc, Fs + r * lds + j0, lds, mr, jw, lane);
         }
         __syncthreads();
@@ -780,7 +817,7 @@ factor_smem_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd
             int mr = min(16, s - r), nc = min(32, s - c);
             Acc<2, 4> acc;
             acc.zero();
-            warp_gemm<2, 4>(acc, Fs + r * lds, lds, mr, Fs + c, lds, nc, k, lane);
+            warp_gemm_shared<2, 4>(acc, Fs + r * lds, lds, mr, Fs + c, lds, nc, k, lane);
             store_tile<2, 4, true>(acc, Fs + r * lds + c, lds, mr, nc, lane);
         }
         __syncthreads();
