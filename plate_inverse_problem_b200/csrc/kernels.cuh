@@ -1253,7 +1253,20 @@ __global__ void spmv_kernel(int N, int64_t nnz, const int* __restrict__ ptr,
     const cd* vb = vals + (int64_t)b * vals_sb * nnz;
     const cd* xb = x + ((int64_t)j * x_sj + (int64_t)b * x_sb) * N;
     cd acc = make_double2(0.0, 0.0);
-    for (int q = ptr[i]; q < ptr[i + 1]; ++q) {
+    // four entries per trip: the index loads, then the value / vector gathers, go out together
+    const int q1 = ptr[i + 1];
+    int q = ptr[i];
+    for (; q + 4 <= q1; q += 4) {
+        int pq[4], jq[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { pq[u] = pos ? __ldg(pos + q + u) : q + u; jq[u] = __ldg(idx + q + u); }
+        cd a[4], xv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { a[u] = vb[pq[u]]; xv[u] = xb[jq[u]]; }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) cfma(acc, a[u], xv[u]);
+    }
+    for (; q < q1; ++q) {
         cd a = vb[pos ? pos[q] : q];
         cfma(acc, a, xb[idx[q]]);
     }
