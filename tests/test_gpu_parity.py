@@ -307,3 +307,48 @@ def test_two_shards_equal_one(small):
         acc[1:] += np.real(np.einsum("fk,fkp->p", ct, dc) + np.einsum("f,fp->p", cts, ds))
     assert abs(acc[0] - L) <= 1e-12 * abs(L)
     assert relerr(acc[1:], g) <= 1e-10
+
+
+_VARIANT_SCRIPT = r"""
+import sys, json, numpy as np
+sys.path.insert(0, {root!r})
+from plate_inverse_problem_b200.Problem import Problem, Geometry, AP1030
+from plate_inverse_problem_b200.Material import SOL
+from plate_inverse_problem_b200.synthetic import make_plate, NAMED_SIZES
+p = np.array([130e9, 9e9, 5e9, 0.3, 0.01])
+prob = Problem(Geometry(2e-3, make_plate(*NAMED_SIZES["cfg0"])), SOL(1600.0, (0, 45, -45, 90), *p), AP1030)
+if {streams} > 1:
+    prob._st.check(prob._st.lib.jpb_set_streams(prob._st.h, {streams}))
+freqs = np.linspace(40.0, 600.0, 70)
+fr = prob.solveForward(freqs)
+L, g = prob.getLossFunction(freqs, fr * (1.0 + 0.1 * np.cos(np.arange(freqs.size))), "MSE").value_and_grad(p)
+print(json.dumps(dict(fr=fr.tolist(), L=float(L), g=np.asarray(g).tolist())))
+"""
+
+
+def _run_variant(env, streams=1):
+    import json
+    import subprocess
+    import sys
+    e = dict(os.environ)
+    e.update(env)
+    out = subprocess.run([sys.executable, "-c", _VARIANT_SCRIPT.format(root=ROOT, streams=streams)], env=e,
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    return json.loads(out.stdout.strip().splitlines()[-1])
+
+
+def test_kernel_variants_agree():
+    """Every front-size class has two kernels (shared-memory-resident vs global-memory fronts in
+    the factorisation, warp-per-system vs CTA-per-front in the triangular solves); the size
+    thresholds are read once per process, so each setting runs in its own interpreter.  All
+    settings must agree on FRF, loss and gradient far inside the parity tolerances, and so must
+    the multi-stream sub-wave schedule."""
+    base = _run_variant({})
+    variants = [({"JPB_SMEM_MAX": "0"}, 1), ({"JPB_SMEM_MAX": "112"}, 1), ({"JPB_WSOLVE_MAX": "0"}, 1),
+                ({"JPB_WSOLVE_MAX": "320"}, 1), ({"JPB_SMEM_STEP": "16", "JPB_FRONT_BIG": "96"}, 1), ({}, 3)]
+    for env, streams in variants:
+        r = _run_variant(env, streams)
+        assert relerr(np.array(r["fr"]), np.array(base["fr"])) <= 1e-9, env
+        assert abs(r["L"] - base["L"]) <= 1e-9 * abs(base["L"]), env
+        assert relerr(np.array(r["g"]), np.array(base["g"])) <= 1e-8, env
