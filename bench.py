@@ -36,8 +36,8 @@ ANGLES = (0, 45, -45, 90)
 FREQS_PER_GPU = {"cfg1": 400, "cfg0": 400, "small": 64, "cfg4": 96, "cfg5": 160, "40k": 256}
 METRIC = "freq-point forward+adjoint+grad evals/s"
 # DRAM bytes moved by the factor launches of one wave, from the committed ncu launch list
-# (profiles/r1h_launches_cfg1_F400.csv: 60.2 + 5.1 GB read, 57.8 + 11.3 GB written)
-FACTOR_DRAM_BYTES = {("cfg1", 400): 134.4e9}
+# (profiles/r1k_launches_cfg1_F400.csv: 43.9 + 4.9 GB read, 40.4 + 9.7 GB written)
+FACTOR_DRAM_BYTES = {("cfg1", 400): 98.9e9}
 
 
 def make_inputs(workload):
@@ -142,24 +142,60 @@ def workload_name(wl):
 
 # ------------------------------------------------------------------------------ clocks
 class ClockSampler:
+    """SM clock and throttle reasons sampled DURING the timed region.  In-process NVML
+    (nvidia_ml_py) when available: forking `nvidia-smi` every 200 ms from a process that holds a
+    CUDA context stalls the host thread for milliseconds at a time and showed up as a 25 %
+    swing of the end-to-end number; the subprocess is only the fallback."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    BITS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20),
+            ("sw_power_cap", 0x4))
 
     def __init__(self, index):
         self.index, self.samples, self.stop = index, [], False
         self.th = threading.Thread(target=self.run, daemon=True)
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(index))
+            self.max_sm = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nvml = None
+
+    @staticmethod
+    def _physical_index(index):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [v.strip() for v in vis.split(",") if v.strip()]
+            if index < len(ids) and ids[index].isdigit():
+                return int(ids[index])
+        return index
+
+    def sample(self):
+        if self.nvml is not None:
+            n = self.nvml
+            sm = float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM))
+            try:
+                mask = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+            except Exception:
+                mask = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+            return [str(sm), str(self.max_sm)] + ["Active" if mask & b else "Not Active" for _, b in self.BITS]
+        out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                              "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                             timeout=5).stdout.strip()
+        return [x.strip() for x in out.split(",")] if out else None
 
     def run(self):
         while not self.stop:
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
-                                     timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([x.strip() for x in out.split(",")])
+                smp = self.sample()
+                if smp:
+                    self.samples.append(smp)
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(0.05 if self.nvml is not None else 0.2)
 
     def __enter__(self):
         self.th.start()
@@ -173,10 +209,11 @@ class ClockSampler:
         if not self.samples:
             return dict(sm_mhz=None, sm_max_mhz=None, reasons=[])
         sm = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        names = [nm for nm, _ in self.BITS]
         reasons = [nm for k, nm in enumerate(names) if any(s[2 + k].lower().startswith("active") for s in self.samples)]
         return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=float(self.samples[0][1]),
-                    reasons=reasons, samples=len(self.samples))
+                    reasons=reasons, samples=len(self.samples),
+                    source="nvml" if self.nvml is not None else "nvidia-smi")
 
 
 # --------------------------------------------------------------------------------- GPU
@@ -311,7 +348,7 @@ def run_ours(args):
                           frac=fac_tf / float(peak[0]),
                           traffic=FACTOR_DRAM_BYTES.get((wl, nloc)),
                           traffic_note="dram__bytes_read+write summed over the factor launches of one "
-                                       "wave (ncu launch list profiles/r1h_launches_cfg1_F400.csv)",
+                                       "wave (ncu launch list profiles/r1k_launches_cfg1_F400.csv)",
                           kernel="numeric factorisation of one wave: factor_smem_kernel (fronts <= 64) + "
                                  "factor_level_kernel (larger fronts), all levels",
                           note="FP64 DMMA (mma.sync m8n8k4) peak measured live by jpb_dmma_peak; "
