@@ -343,7 +343,14 @@ __device__ __forceinline__ cd pivot_reciprocal(cd z, unsigned key) {
     const int ex = ((int)(key >> 21)) - 1023;
     const double sc = __hiloint2double((1023 - ex) << 20, 0);   // 2^-ex, exact
     const double zx = z.x * sc, zy = z.y * sc;
-    const double q = sc / fma(zx, zx, zy * zy);
+    // |z|^2 of the scaled pivot lies in [1, 8): the hardware reciprocal seed plus two Newton
+    // steps is accurate to the last bit or two and a third of the dependent chain of a division
+    const double n2 = fma(zx, zx, zy * zy);
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(n2));
+    r = fma(fma(-n2, r, 1.0), r, r);
+    r = fma(fma(-n2, r, 1.0), r, r);
+    const double q = sc * r;
     return make_double2(zx * q, -zy * q);
 }
 
