@@ -418,10 +418,12 @@ __device__ __forceinline__ int invert_tile(TileSmem& ts, int n, int tid) {
                     if (lane == p) out = make_double2(0.0, 0.0);
                     out.x = fma(-f[u].x, rb.x, out.x); out.x = fma(f[u].y, rb.y, out.x);
                     out.y = fma(-f[u].x, rb.y, out.y); out.y = fma(-f[u].y, rb.x, out.y);
-                    if (i == p) out = rb;
                     if (i < n) Dn[i * TLD + lane] = out;
                 }
             }
+            // row p = the normalised pivot row, written after (and by the warp of) the loop's
+            // meaningless update of that row: no per-element select on the row index
+            if (warp == p % NW) Dn[p * TLD + lane] = rb;
         }
         __syncthreads();
         cur ^= 1;
@@ -648,8 +650,15 @@ __device__ __forceinline__ void invert_tile_inplace(cd* T, int ldt, int n, int t
         const cd d = ok ? pivot_reciprocal(T[r * ldt + p], key) : make_double2(1.0, 0.0);
         const cd rb = (lane == p) ? d : cmul(T[r * ldt + jl], d);
         const cd pr = T[p * ldt + jl];
-        const cd fpp = T[p * ldt + p];
         __syncthreads();
+        // Rows p and r trade places: the owner warp of row r first drops the old row p into it
+        // (everybody holds what they need of the old rows p and r in registers), after which
+        // every row but p takes the same update; row p is written last, by its owner warp.
+        // No per-element selects on the row index are left in the loop.
+        if (r != p && warp == r % NW) {
+            if (lane < n) T[r * ldt + lane] = pr;
+            __syncwarp();
+        }
         for (int i0 = warp; i0 < n; i0 += 4 * NW) {      // four rows per trip (see invert_tile)
             cd f[4], a[4];
 #pragma unroll
@@ -657,7 +666,6 @@ __device__ __forceinline__ void invert_tile_inplace(cd* T, int ldt, int n, int t
                 const int i = min(i0 + u * NW, n - 1);
                 f[u] = T[i * ldt + p];
                 a[u] = T[i * ldt + jl];
-                if (i == r) { f[u] = fpp; a[u] = pr; }
             }
             __syncwarp();      // every lane has read T[i][p] before lane p overwrites it
 #pragma unroll
@@ -667,9 +675,12 @@ __device__ __forceinline__ void invert_tile_inplace(cd* T, int ldt, int n, int t
                 if (lane == p) out = make_double2(0.0, 0.0);
                 out.x = fma(-f[u].x, rb.x, out.x); out.x = fma(f[u].y, rb.y, out.x);
                 out.y = fma(-f[u].x, rb.y, out.y); out.y = fma(-f[u].y, rb.x, out.y);
-                if (i == p) out = rb;
                 if (i < n && lane < n) T[i * ldt + lane] = out;
             }
+        }
+        if (warp == p % NW) {      // same warp that just stored row p's (meaningless) update
+            __syncwarp();
+            if (lane < n) T[p * ldt + lane] = rb;
         }
         __syncthreads();
     }
@@ -830,10 +841,15 @@ factor_smem_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd
         __syncthreads();
     }
     // the finished front leaves in one pass: warp per row, lanes along the row
-    for (int i = warp; i < s; i += NW) {
-        const cd* src = Fs + i * lds;
-        cd* dst = Fg + (int64_t)i * ld;
-        for (int j = lane; j < s; j += 32) dst[j] = src[j];
+    for (int j = lane; j < s; j += 32) {
+        for (int i0 = warp; i0 < s; i0 += 4 * NW) {      // four rows in flight per lane
+            cd v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = Fs[min(i0 + u * NW, s - 1) * lds + j];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (i0 + u * NW < s) Fg[(int64_t)(i0 + u * NW) * ld + j] = v[u];
+        }
     }
     if (tid == 0 && ps.sing && status) atomicOr(status + b, 1);
 }
