@@ -407,9 +407,8 @@ __device__ __forceinline__ int invert_tile(TileSmem& ts, int n, int tid) {
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     const int i = min(i0 + u * NW, n - 1);
-                    const int oi = (i == r) ? p : i;     // rows p and r trade places
-                    f[u] = Dp[oi * TLD];
-                    a[u] = Dl[oi * TLD];
+                    f[u] = Dp[i * TLD];
+                    a[u] = Dl[i * TLD];
                 }
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
@@ -421,8 +420,17 @@ __device__ __forceinline__ int invert_tile(TileSmem& ts, int n, int tid) {
                     if (i < n) Dn[i * TLD + lane] = out;
                 }
             }
-            // row p = the normalised pivot row, written after (and by the warp of) the loop's
-            // meaningless update of that row: no per-element select on the row index
+            // rows p and r trade places: row r receives the update of the OLD row p, row p the
+            // normalised pivot row; both are written after (and by the warps of) the loop's
+            // meaningless updates of those rows, which keeps the loop free of row selects
+            if (r != p && warp == r % NW) {
+                const cd f = Dp[p * TLD];
+                cd out = Dl[p * TLD];
+                if (lane == p) out = make_double2(0.0, 0.0);
+                out.x = fma(-f.x, rb.x, out.x); out.x = fma(f.y, rb.y, out.x);
+                out.y = fma(-f.x, rb.y, out.y); out.y = fma(-f.y, rb.x, out.y);
+                Dn[r * TLD + lane] = out;
+            }
             if (warp == p % NW) Dn[p * TLD + lane] = rb;
         }
         __syncthreads();
