@@ -462,6 +462,9 @@ constexpr int KMAX = 32;   // component matrices supported by the fused assembly
 #ifndef JPB_OCC
 #define JPB_OCC 512
 #endif
+#ifndef JPB_STRIP_WN
+#define JPB_STRIP_WN 2
+#endif
 template <bool ENT_ORDER, int NT>
 __global__ void __launch_bounds__(NT, JPB_OCC / NT)
 factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd* Fall,
@@ -546,25 +549,29 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
         const int j1 = j0 + jw;
         if (J > 0) {
             // column strip rows [j0,s) x cols [j0,j1) and row strip rows [j0,j1) x cols [j1,s)
-            const int nct = ((s - j0 + 15) >> 4) * (TW / WC);
+            // warp tiles of 16 x 16 here (SN = 2 accumulator blocks across): with the live state
+            // of the tile loop around it the 16 x 32 tile made ptxas spill inside the k-loop
+            constexpr int SN = JPB_STRIP_WN, SC = 8 * SN, CT = TW / SC;
+            const int nct = ((s - j0 + 15) >> 4) * CT;
             const int nrr = (jw + 15) >> 4;
-            const int nrc = (s - j1 + WC - 1) / WC;
+            const int nrc = (s - j1 + SC - 1) / SC;
             const int ntiles = nct + nrr * nrc;
             for (int tile = warp; tile < ntiles; tile += NW) {
                 int r, c, mr, nc;
                 if (tile < nct) {
-                    const int rt = tile / (TW / WC), ct = tile % (TW / WC);
-                    r = j0 + 16 * rt; c = j0 + WC * ct; mr = min(16, s - r); nc = min(WC, j1 - c);
+                    const int rt = tile / CT, ct = tile % CT;
+                    r = j0 + 16 * rt; c = j0 + SC * ct; mr = min(16, s - r); nc = min(SC, j1 - c);
                 } else {
                     int q = tile - nct;
-                    r = j0 + 16 * (q % nrr); c = j1 + WC * (q / nrr);
-                    mr = min(16, j1 - r); nc = min(WC, s - c);
+                    r = j0 + 16 * (q % nrr); c = j1 + SC * (q / nrr);
+                    mr = min(16, j1 - r); nc = min(SC, s - c);
                 }
-                Acc<2, WN> acc;
+                if (nc <= 0) continue;
+                Acc<2, SN> acc;
                 acc.zero();
-                prefetch_tile<WN>(F + (int64_t)r * ld + c, ld, mr, nc, lane);
-                warp_gemm<2, WN>(acc, F + (int64_t)r * ld, ld, mr, F + c, ld, nc, j0, lane);
-                store_tile<2, WN, true>(acc, F + (int64_t)r * ld + c, ld, mr, nc, lane);
+                prefetch_tile<SN>(F + (int64_t)r * ld + c, ld, mr, nc, lane);
+                warp_gemm<2, SN>(acc, F + (int64_t)r * ld, ld, mr, F + c, ld, nc, j0, lane);
+                store_tile<2, SN, true>(acc, F + (int64_t)r * ld + c, ld, mr, nc, lane);
             }
             __syncthreads();
         }
