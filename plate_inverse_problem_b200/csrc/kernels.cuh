@@ -1209,7 +1209,7 @@ fwd_warp_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __res
 #define JPB_BWD_OCC 4
 #endif
 template <bool TRANS, int NW>
-__global__ void __launch_bounds__(NW * 32, TRANS ? 5 : JPB_BWD_OCC)
+__global__ void __launch_bounds__(NW * 32, TRANS ? 4 : JPB_BWD_OCC)
 bwd_warp_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __restrict__ Fall,
                 VecView vv, int vstride) {
     extern __shared__ cd vsm[];
