@@ -457,7 +457,7 @@ constexpr int KMAX = 32;   // component matrices supported by the fused assembly
 //                  also stored to vals[b, q] for the residual kernels
 //   FUSED = false: A entries are data[b, ent_src[q]]
 #ifndef JPB_WN
-#define JPB_WN 4
+#define JPB_WN 2     // measured: 16 x 16 warp tiles (no spills) beat 16 x 32 at cfg1 and tie at cfg4
 #endif
 #ifndef JPB_OCC
 #define JPB_OCC 512
@@ -472,7 +472,9 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
     __shared__ TileSmem ts;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = NT / 32;
-    constexpr int WN = JPB_WN, WC = 8 * WN;   // warp tile: 16 rows x WC columns
+    // warp tile: 16 rows x WC columns.  JPB_WN = 0: 16 x 32 for the 256-thread class (operand reuse
+    // on the large fronts), 16 x 16 for the narrower ones (no register spills, more tiles per warp)
+    constexpr int WN = JPB_WN ? JPB_WN : (NT == 256 ? 4 : 2), WC = 8 * WN;
     constexpr int FACTOR_THREADS = NT;
     const int b = blockIdx.x % nsys;
     const FrontDesc fd = sd.fr[level_fronts[blockIdx.x / nsys]];
