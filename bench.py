@@ -36,8 +36,8 @@ ANGLES = (0, 45, -45, 90)
 FREQS_PER_GPU = {"cfg1": 400, "cfg0": 400, "small": 64, "cfg4": 96, "cfg5": 160, "40k": 256}
 METRIC = "freq-point forward+adjoint+grad evals/s"
 # DRAM bytes moved by the factor launches of one wave, from the committed ncu launch list
-# (profiles/r1m_launches_cfg1_F400.csv: 44.0 + 4.9 GB read, 40.2 + 9.7 GB written)
-FACTOR_DRAM_BYTES = {("cfg1", 400): 98.8e9}
+# (profiles/r1n_launches_cfg1_F400.csv: 40.6 + 4.9 GB read, 36.8 + 9.7 GB written)
+FACTOR_DRAM_BYTES = {("cfg1", 400): 92.0e9}
 
 
 def make_inputs(workload):
@@ -352,7 +352,7 @@ def run_ours(args):
                           frac=fac_tf / float(peak[0]),
                           traffic=FACTOR_DRAM_BYTES.get((wl, nloc)),
                           traffic_note="dram__bytes_read+write summed over the factor launches of one "
-                                       "wave (ncu launch list profiles/r1m_launches_cfg1_F400.csv)",
+                                       "wave (ncu launch list profiles/r1n_launches_cfg1_F400.csv)",
                           kernel="numeric factorisation of one wave: factor_smem_kernel (fronts <= 64) + "
                                  "factor_level_kernel (larger fronts), all levels",
                           note="FP64 DMMA (mma.sync m8n8k4) peak measured live by jpb_dmma_peak; "
