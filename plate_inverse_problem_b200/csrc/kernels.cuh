@@ -383,6 +383,10 @@ template <int NT>
 __device__ __forceinline__ int invert_tile(TileSmem& ts, int n, int tid) {
     const int lane = tid & 31, warp = tid >> 5;
     constexpr int NW = NT / 32;
+    constexpr int R = TW / NW;        // rows of a thread: warp, warp + NW, ... (fixed over the pivots)
+    int roff[R];
+#pragma unroll
+    for (int u = 0; u < R; ++u) roff[u] = min(warp + u * NW, n - 1) * TLD;
     int cur = 0;
     for (int p = 0; p < n; ++p) {
         const cd* Dc = &ts.D[cur][0][0];
@@ -399,25 +403,32 @@ __device__ __forceinline__ int invert_tile(TileSmem& ts, int n, int tid) {
         if (lane < n) {
             const cd rb = (lane == p) ? d : cmul(Dc[r * TLD + lane], d);
             // four rows per trip: the eight shared loads go out together and the four FMA
-            // chains interleave (a warp's progress here is bounded by dependent-issue latency)
+            // chains interleave (a warp's progress here is bounded by dependent-issue latency);
+            // the row offsets are per-thread constants, so the loop carries no index arithmetic
             const cd* Dl = Dc + lane;
             const cd* Dp = Dc + p;
-            for (int i0 = warp; i0 < n; i0 += 4 * NW) {
-                cd f[4], a[4];
+            cd* Dnl = Dn + lane;
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int i = min(i0 + u * NW, n - 1);
-                    f[u] = Dp[i * TLD];
-                    a[u] = Dl[i * TLD];
-                }
+            for (int ub = 0; ub < R; ub += 4) {
+                if (warp + ub * NW < n) {
+                    cd f[4], a[4];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int i = i0 + u * NW;
-                    cd out = a[u];
-                    if (lane == p) out = make_double2(0.0, 0.0);
-                    out.x = fma(-f[u].x, rb.x, out.x); out.x = fma(f[u].y, rb.y, out.x);
-                    out.y = fma(-f[u].x, rb.y, out.y); out.y = fma(-f[u].y, rb.x, out.y);
-                    if (i < n) Dn[i * TLD + lane] = out;
+                    for (int u = 0; u < 4; ++u) {
+                        if (ub + u < R) {
+                            f[u] = Dp[roff[ub + u]];
+                            a[u] = Dl[roff[ub + u]];
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        if (ub + u < R) {
+                            cd out = a[u];
+                            if (lane == p) out = make_double2(0.0, 0.0);
+                            out.x = fma(-f[u].x, rb.x, out.x); out.x = fma(f[u].y, rb.y, out.x);
+                            out.y = fma(-f[u].x, rb.y, out.y); out.y = fma(-f[u].y, rb.x, out.y);
+                            if (warp + (ub + u) * NW < n) Dnl[roff[ub + u]] = out;
+                        }
+                    }
                 }
             }
             // rows p and r trade places: row r receives the update of the OLD row p, row p the
@@ -654,7 +665,11 @@ template <int NT>
 __device__ __forceinline__ void invert_tile_inplace(cd* T, int ldt, int n, int tid, PivotSmem& ps) {
     const int lane = tid & 31, warp = tid >> 5;
     constexpr int NW = NT / 32;
+    constexpr int R = TW / NW;        // rows of a thread: warp, warp + NW, ... (fixed over the pivots)
     const int jl = min(lane, n - 1);
+    int roff[R];
+#pragma unroll
+    for (int u = 0; u < R; ++u) roff[u] = min(warp + u * NW, n - 1) * ldt;
     for (int p = 0; p < n; ++p) {
         const unsigned key = pivot_search(T, ldt, n, p, lane);
         const bool ok = (key >> 5) != 0u;
@@ -671,28 +686,35 @@ __device__ __forceinline__ void invert_tile_inplace(cd* T, int ldt, int n, int t
         // Rows p and r trade places: the owner warp of row r first drops the old row p into it
         // (everybody holds what they need of the old rows p and r in registers), after which
         // every row but p takes the same update; row p is written last, by its owner warp.
-        // No per-element selects on the row index are left in the loop.
+        // No per-element selects on the row index and no index arithmetic are left in the loop.
         if (r != p && warp == r % NW) {
             if (lane < n) T[r * ldt + lane] = pr;
             __syncwarp();
         }
-        for (int i0 = warp; i0 < n; i0 += 4 * NW) {      // four rows per trip (see invert_tile)
-            cd f[4], a[4];
+        const cd* Tp = T + p;
+        cd* Tl = T + jl;
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int i = min(i0 + u * NW, n - 1);
-                f[u] = T[i * ldt + p];
-                a[u] = T[i * ldt + jl];
-            }
-            __syncwarp();      // every lane has read T[i][p] before lane p overwrites it
+        for (int ub = 0; ub < R; ub += 4) {      // four rows per trip (see invert_tile)
+            if (warp + ub * NW < n) {
+                cd f[4], a[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int i = i0 + u * NW;
-                cd out = a[u];
-                if (lane == p) out = make_double2(0.0, 0.0);
-                out.x = fma(-f[u].x, rb.x, out.x); out.x = fma(f[u].y, rb.y, out.x);
-                out.y = fma(-f[u].x, rb.y, out.y); out.y = fma(-f[u].y, rb.x, out.y);
-                if (i < n && lane < n) T[i * ldt + lane] = out;
+                for (int u = 0; u < 4; ++u) {
+                    if (ub + u < R) {
+                        f[u] = Tp[roff[ub + u]];
+                        a[u] = Tl[roff[ub + u]];
+                    }
+                }
+                __syncwarp();      // every lane has read T[i][p] before lane p overwrites it
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (ub + u < R) {
+                        cd out = a[u];
+                        if (lane == p) out = make_double2(0.0, 0.0);
+                        out.x = fma(-f[u].x, rb.x, out.x); out.x = fma(f[u].y, rb.y, out.x);
+                        out.y = fma(-f[u].x, rb.y, out.y); out.y = fma(-f[u].y, rb.x, out.y);
+                        if (warp + (ub + u) * NW < n && lane < n) Tl[roff[ub + u]] = out;
+                    }
+                }
             }
         }
         if (warp == p % NW) {      // same warp that just stored row p's (meaningless) update
