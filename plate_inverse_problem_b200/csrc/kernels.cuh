@@ -258,10 +258,17 @@ __device__ __forceinline__ void store_tile(const Acc<MB, NB>& acc, cd* C, int ld
 // Epilogue of a contribution-block tile: C(i, j) = sum_children child(inv_c[i], inv_c[j]) - P(i, j)
 // with P the accumulated product Lt * U.  (rc, cc) is the tile's position inside the block;
 // every element of the block is written exactly once and never read here.
+struct ChildInfo {      // what the gather needs of a child, staged once per CTA in shared memory
+    int64_t cb;         // slot of the child's contribution block inside the system's front storage
+    int ld;
+    int invoff;
+};
+constexpr int MAXCH = 8;
+
 template <int MB, int NB>
 __device__ __forceinline__ void store_tile_cb(const Acc<MB, NB>& acc, cd* C, int ldc, int mrows, int ncols,
                                               int rc, int cc, const SymDev& sd, const FrontDesc& fd,
-                                              const cd* Fsys, int lane) {
+                                              const ChildInfo* chs, const cd* Fsys, int lane) {
     const int g = lane >> 2, t = lane & 3;
     cd val[MB][NB][2];
 #pragma unroll
@@ -271,9 +278,17 @@ __device__ __forceinline__ void store_tile_cb(const Acc<MB, NB>& acc, cd* C, int
 #pragma unroll
             for (int e = 0; e < 2; ++e) val[m][n][e] = make_double2(-acc.re[m][n][e], -acc.im[m][n][e]);
     for (int ci = 0; ci < fd.nchild; ++ci) {
-        const FrontDesc fc = sd.fr[sd.children[fd.childptr + ci]];
-        const int* inv = sd.cbinv + fc.invoff;
-        const cd* Fc = Fsys + fc.off + (int64_t)fc.k * fc.ld + fc.k;
+        ChildInfo ch;
+        if (fd.nchild <= MAXCH) {
+            ch = chs[ci];
+        } else {
+            const FrontDesc fc = sd.fr[sd.children[fd.childptr + ci]];
+            ch.cb = fc.off + (int64_t)fc.k * fc.ld + fc.k;
+            ch.ld = fc.ld;
+            ch.invoff = fc.invoff;
+        }
+        const int* inv = sd.cbinv + ch.invoff;
+        const cd* Fc = Fsys + ch.cb;
         int ri[MB], cj[NB][2];
 #pragma unroll
         for (int m = 0; m < MB; ++m) ri[m] = 8 * m + g < mrows ? __ldg(inv + rc + 8 * m + g) : -1;
@@ -285,7 +300,7 @@ __device__ __forceinline__ void store_tile_cb(const Acc<MB, NB>& acc, cd* C, int
 #pragma unroll
         for (int m = 0; m < MB; ++m) {
             if (ri[m] < 0) continue;
-            const cd* row = Fc + (int64_t)ri[m] * fc.ld;
+            const cd* row = Fc + (int64_t)ri[m] * ch.ld;
 #pragma unroll
             for (int n = 0; n < NB; ++n)
 #pragma unroll
@@ -502,7 +517,14 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
     cd* F = Fsys + fd.off;
     const int s = fd.s, k = fd.k, ld = fd.ld;
 
+    __shared__ ChildInfo chs[MAXCH];
     if (tid == 0) { ts.sing = 0; ts.swapped = 0; }
+    if (tid < fd.nchild && tid < MAXCH) {
+        const FrontDesc fc = sd.fr[sd.children[fd.childptr + tid]];
+        chs[tid].cb = fc.off + (int64_t)fc.k * fc.ld + fc.k;
+        chs[tid].ld = fc.ld;
+        chs[tid].invoff = fc.invoff;
+    }
     // ---- zero, then A entries (every entry owns its slot), then the children one by one
     // Only the pivot rows and pivot columns are assembled by zero + scatter; the contribution
     // block (rows and columns >= k) is written exactly once, by the Schur phase, which gathers
@@ -640,7 +662,7 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
             Acc<2, WN> acc;
             acc.zero();
             warp_gemm<2, WN>(acc, F + (int64_t)r * ld, ld, mr, F + c, ld, nc, k, lane);
-            store_tile_cb<2, WN>(acc, F + (int64_t)r * ld + c, ld, mr, nc, rc, cc, sd, fd, Fsys, lane);
+            store_tile_cb<2, WN>(acc, F + (int64_t)r * ld + c, ld, mr, nc, rc, cc, sd, fd, chs, Fsys, lane);
         }
     }
     if (tid == 0 && ts.sing && status) atomicOr(status + b, 1);
