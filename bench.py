@@ -33,6 +33,7 @@ sys.path.insert(0, ROOT)
 H, RHO = 2e-3, 1600.0
 PARAMS = np.array([130e9, 9e9, 5e9, 0.3, 0.01])
 ANGLES = (0, 45, -45, 90)
+E2E_WARMUP = 8
 FREQS_PER_GPU = {"cfg1": 400, "cfg0": 400, "small": 64, "cfg4": 96, "cfg5": 160, "40k": 256}
 METRIC = "freq-point forward+adjoint+grad evals/s"
 # DRAM bytes moved by the factor launches of one wave, from the committed ncu launch list
@@ -301,21 +302,30 @@ def run_ours(args):
         ms_dev, acc = timed(step_device, args.steps)
         tm = st.timings()      # phase timers of the last step (CUDA events on the same stream)
         # ---- end-to-end arm: public API, host buffers, H2D + D2H inside the timed region ---
-        for _ in range(max(1, min(args.warmup, 2))):
+        # the host side of the public call (torch autograd of the material transform, ctypes,
+        # pinned staging) needs a few more calls than the kernels to reach steady state on a
+        # fresh box (observed 137 -> 107 -> 97 -> 80 ms over the first calls after 3 warm-ups)
+        for _ in range(max(args.warmup, E2E_WARMUP)):
             loss.value_and_grad(PARAMS)
         barrier()
         import gc
         gc.collect()
         gc.disable()          # as timeit does: no collector pause inside the timed region
         t0 = time.perf_counter()
+        trace, devms = [], []
         for _ in range(args.steps):
             L_e2e, g_e2e = loss.value_and_grad(PARAMS)
+            trace.append(time.perf_counter())
+            if os.environ.get("JPB_E2E_TRACE"):
+                devms.append(round(sum(v for k, v in st.timings().items() if k.endswith("_ms")), 1))
         torch.cuda.synchronize()
         dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
         gc.enable()
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e_s = dt.item()
+        if os.environ.get("JPB_E2E_TRACE"):
+            print("e2e per-step ms:", np.round(np.diff([t0] + trace) * 1e3, 1), "device ms:", devms, file=sys.stderr)
     acc = acc.cpu().numpy()
     assert np.allclose(acc[0], L_e2e, rtol=1e-9) and np.allclose(acc[1:], g_e2e, rtol=1e-7, atol=1e-12 * np.abs(g_e2e).max())
     assert int(d_stat.max().item()) == 0
@@ -344,8 +354,10 @@ def run_ours(args):
                         l2_policy="working set (fronts of one wave, %.1f GB) far exceeds the 126 MB L2; no flush needed"
                                   % (info["front_slots"] * 16 * min(nloc, tm["wave"]) / 1e9)),
             e2e=dict(value=e2e_value, unit="evals/s",
-                     h2d_bytes_per_step=int(nloc * (K * 16 + 16 + 8) + 24),
-                     d2h_bytes_per_step=int(nloc * (8 + K * 16 + 16 + 4) + 8)),
+                     # the two pinned-staging transfers of jpb_eval_loss_grad (engine.cu)
+                     h2d_bytes_per_step=int((nloc * (K * 16 + 16 + 8) + 32 + 15) // 16 * 16),
+                     d2h_bytes_per_step=int(nloc * (K * 16 + 16 + 8 + 4) + 16),
+                     warmup=max(args.warmup, E2E_WARMUP)),
             gpu_launches=int(tm["launches"] * args.steps),
             clocks=clocks.summary(),
             roofline=dict(bound="tensor", achieved=fac_tf, peak=float(peak[0]), unit="TFLOP/s",

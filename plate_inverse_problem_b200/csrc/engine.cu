@@ -71,6 +71,28 @@ struct DevBuf {
     ~DevBuf() { release(); }
 };
 
+// page-locked host mirror of a device staging block: the caller's (pageable) arrays are
+// copied through it so the transfers are true asynchronous DMA, one per direction
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    void* get(size_t bytes) {
+        if (bytes > cap) {
+            if (p) cudaFreeHost(p);
+            p = nullptr;
+            cap = 0;
+            if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+                p = nullptr;
+                throw CudaError("cudaHostAlloc of the staging mirror failed");
+            }
+            cap = bytes;
+        }
+        return p;
+    }
+    ~PinBuf() { if (p) cudaFreeHost(p); }
+};
+
+
 template <class T>
 T* upload(const std::vector<T>& v) {
     T* d = nullptr;
@@ -136,6 +158,7 @@ struct jpb_state {
     int refine = 1;
     // workspaces
     DevBuf F, V, vals, data, vb, vx, vr, vd, vlam, partial, small, hstage, status;
+    PinBuf pin;
     // instrumentation
     std::vector<TimedSpan> spans;
     std::vector<cudaEvent_t> pool;
@@ -1104,40 +1127,47 @@ int jpb_eval_loss_grad(jpb_state* st, int solver_num, int64_t B, const double* c
     st->reset_timing();
     cudaStream_t s = st->stream;
     const int K = P.K, R = P.R;
-    // device staging: coef [B,K] c, scale [B] c, y [B,R] c, ct_coef [B,K] c, ct_s [B] c,
-    // ref [B] d, fr [B] d, w [R] d, loss d, status [B] i
-    size_t nc = (size_t)B * (2 * K + 2 + R);
-    size_t bytes = nc * 16 + (size_t)B * 16 + 64 + (size_t)B * 4 + 64;
-    char* stage = (char*)st->hstage.get(bytes);
+    // device staging block, inputs first and results last so that each direction is one copy:
+    //   in : coef [B,K] c, scale [B] c, ref [B] d, w [4] d
+    //   -- : y [B,R] c (device only)
+    //   out: ct_coef [B,K] c, ct_s [B] c, fr [B] d, loss [2] d, status [B] i
+    const size_t in_bytes = ((size_t)B * (K * 16 + 16 + 8) + 32 + 15) & ~(size_t)15;
+    const size_t y_bytes = (size_t)B * R * 16;
+    const size_t out_bytes = (size_t)B * (K * 16 + 16 + 8 + 4) + 16;
+    char* stage = (char*)st->hstage.get(in_bytes + y_bytes + out_bytes + 64);
+    char* pin = (char*)st->pin.get(in_bytes + out_bytes);
     cd* dcoef = (cd*)stage;
     cd* dscale = dcoef + B * K;
-    cd* dy = dscale + B;
-    cd* dct = dy + B * R;
+    double* dref = (double*)(dscale + B);
+    double* dw = dref + B;
+    cd* dy = (cd*)(stage + in_bytes);
+    char* dout = stage + in_bytes + y_bytes;
+    cd* dct = (cd*)dout;
     cd* dcts = dct + B * K;
-    double* dref = (double*)(dcts + B);
-    double* dfr = dref + B;
-    double* dw = dfr + B;
-    double* dloss = dw + 4;
+    double* dfr = (double*)(dcts + B);
+    double* dloss = dfr + B;
     int* dstat = (int*)(dloss + 2);
     {
         Span span(st, s, PH_H2D);
-        CK(cudaMemcpyAsync(dcoef, coef, (size_t)B * K * 16, cudaMemcpyHostToDevice, s));
-        CK(cudaMemcpyAsync(dscale, rhs_scale, (size_t)B * 16, cudaMemcpyHostToDevice, s));
-        CK(cudaMemcpyAsync(dref, ref, (size_t)B * 8, cudaMemcpyHostToDevice, s));
-        CK(cudaMemcpyAsync(dw, w, (size_t)R * 8, cudaMemcpyHostToDevice, s));
+        memcpy(pin, coef, (size_t)B * K * 16);
+        memcpy(pin + ((char*)dscale - stage), rhs_scale, (size_t)B * 16);
+        memcpy(pin + ((char*)dref - stage), ref, (size_t)B * 8);
+        memcpy(pin + ((char*)dw - stage), w, (size_t)R * 8);
+        CK(cudaMemcpyAsync(stage, pin, in_bytes, cudaMemcpyHostToDevice, s));
     }
     eval_core(st, s, P, B, dcoef, dscale, dref, dw, loss_type, F_total, nullptr, dy, dfr, dloss, dct, dcts,
               dstat, true);
-    std::vector<int> hstat(B);
+    char* pout = pin + in_bytes;
     {
         Span span(st, s, PH_D2H);
-        CK(cudaMemcpyAsync(fr, dfr, (size_t)B * 8, cudaMemcpyDeviceToHost, s));
-        CK(cudaMemcpyAsync(loss_sum, dloss, 8, cudaMemcpyDeviceToHost, s));
-        CK(cudaMemcpyAsync(ct_coef, dct, (size_t)B * K * 16, cudaMemcpyDeviceToHost, s));
-        CK(cudaMemcpyAsync(ct_s, dcts, (size_t)B * 16, cudaMemcpyDeviceToHost, s));
-        CK(cudaMemcpyAsync(hstat.data(), dstat, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(pout, dout, out_bytes, cudaMemcpyDeviceToHost, s));
     }
     CK(cudaStreamSynchronize(s));
+    memcpy(ct_coef, pout, (size_t)B * K * 16);
+    memcpy(ct_s, pout + ((char*)dcts - dout), (size_t)B * 16);
+    memcpy(fr, pout + ((char*)dfr - dout), (size_t)B * 8);
+    memcpy(loss_sum, pout + ((char*)dloss - dout), 8);
+    const int* hstat = (const int*)(pout + ((char*)dstat - dout));
     int bad = 0;
     for (int64_t i = 0; i < B; ++i) {
         if (status) status[i] = hstat[i];
