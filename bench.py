@@ -37,8 +37,8 @@ E2E_WARMUP = 8
 FREQS_PER_GPU = {"cfg1": 400, "cfg0": 400, "small": 64, "cfg4": 96, "cfg5": 160, "40k": 256}
 METRIC = "freq-point forward+adjoint+grad evals/s"
 # DRAM bytes moved by the factor launches of one wave, from the committed ncu launch list
-# (profiles/r1n_launches_cfg1_F400.csv: 40.6 + 4.9 GB read, 36.8 + 9.7 GB written)
-FACTOR_DRAM_BYTES = {("cfg1", 400): 92.0e9}
+# (profiles/r1o_launches_cfg1_F400.csv: 40.4 + 4.9 GB read, 36.6 + 9.7 GB written)
+FACTOR_DRAM_BYTES = {("cfg1", 400): 91.6e9}
 
 
 def make_inputs(workload):
@@ -364,7 +364,7 @@ def run_ours(args):
                           frac=fac_tf / float(peak[0]),
                           traffic=FACTOR_DRAM_BYTES.get((wl, nloc)),
                           traffic_note="dram__bytes_read+write summed over the factor launches of one "
-                                       "wave (ncu launch list profiles/r1n_launches_cfg1_F400.csv)",
+                                       "wave (ncu launch list profiles/r1o_launches_cfg1_F400.csv)",
                           kernel="numeric factorisation of one wave: factor_smem_kernel (fronts <= 64) + "
                                  "factor_level_kernel (larger fronts), all levels",
                           note="FP64 DMMA (mma.sync m8n8k4) peak measured live by jpb_dmma_peak; "
