@@ -154,6 +154,7 @@ class ClockSampler:
 
     def __init__(self, index):
         self.index, self.samples, self.stop = index, [], False
+        self.query_ms, self.interval = 0.0, 0.2
         self.th = threading.Thread(target=self.run, daemon=True)
         self.nvml = None
         try:
@@ -164,6 +165,7 @@ class ClockSampler:
             self.max_sm = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
         except Exception:
             self.nvml = None
+        self.interval = float(os.environ.get("JPB_CLOCK_INTERVAL", 0.1 if self.nvml is not None else 0.2))
 
     @staticmethod
     def _physical_index(index):
@@ -191,12 +193,14 @@ class ClockSampler:
     def run(self):
         while not self.stop:
             try:
+                t0 = time.perf_counter()
                 smp = self.sample()
+                self.query_ms = max(self.query_ms, (time.perf_counter() - t0) * 1e3)
                 if smp:
                     self.samples.append(smp)
             except Exception:
                 pass
-            time.sleep(0.1 if self.nvml is not None else 0.2)
+            time.sleep(self.interval)
 
     def __enter__(self):
         self.th.start()
@@ -213,7 +217,7 @@ class ClockSampler:
         names = [nm for nm, _ in self.BITS]
         reasons = [nm for k, nm in enumerate(names) if any(s[2 + k].lower().startswith("active") for s in self.samples)]
         return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=float(self.samples[0][1]),
-                    reasons=reasons, samples=len(self.samples),
+                    reasons=reasons, samples=len(self.samples), max_query_ms=round(self.query_ms, 2),
                     source="nvml" if self.nvml is not None else "nvidia-smi")
 
 
