@@ -283,12 +283,15 @@ def run_ours(args):
     def timed(fn, steps):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
         e0.record()
         out = None
-        for _ in range(steps):
+        for k in range(steps):
             out = fn()
+            marks[k].record()      # per-step boundaries (diagnostic only; the metric uses e0 -> e1)
         e1.record()
         barrier()
+        timed.step_ms = [round(a.elapsed_time(b), 2) for a, b in zip([e0] + marks[:-1], marks)]
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -304,6 +307,7 @@ def run_ours(args):
         step_device()
     with ClockSampler(local) as clocks:
         ms_dev, acc = timed(step_device, args.steps)
+        step_ms = timed.step_ms
         tm = st.timings()      # phase timers of the last step (CUDA events on the same stream)
         # ---- end-to-end arm: public API, host buffers, H2D + D2H inside the timed region ---
         # the host side of the public call (torch autograd of the material transform, ctypes,
@@ -363,6 +367,7 @@ def run_ours(args):
                      d2h_bytes_per_step=int(nloc * (K * 16 + 16 + 8 + 4) + 16),
                      warmup=max(args.warmup, E2E_WARMUP)),
             gpu_launches=int(tm["launches"] * args.steps),
+            step_ms=step_ms,
             clocks=clocks.summary(),
             roofline=dict(bound="tensor", achieved=fac_tf, peak=float(peak[0]), unit="TFLOP/s",
                           frac=fac_tf / float(peak[0]),
