@@ -116,7 +116,10 @@ int jpb_eval_forward(jpb_state* st, int solver_num, int64_t B, const double* coe
  *   fr[B] real; loss_sum = sum_b loss term (caller divides by F_total);
  *   ct_coef[B,K] complex = -lambda_b^T M_k u_b ; ct_s[B] complex = lambda_b^T rhs_vec
  * with lambda_b = A_b^-T ubar_b, ubar_b the JAX-convention cotangent of u_b
- * (SURVEY App. D).  One numeric factorisation per system serves both solves. */
+ * (SURVEY App. D).  One numeric factorisation per system serves both solves.
+ * All arrays are HOST memory (any alignment, pageable is fine): inputs are packed into a
+ * page-locked mirror owned by the state and go to the device in one asynchronous copy,
+ * results come back the same way; the call returns after the stream has drained. */
 int jpb_eval_loss_grad(jpb_state* st, int solver_num, int64_t B, const double* coef,
                        const double* rhs_scale, const double* ref, const double* w,
                        int loss_type, int64_t F_total, double* fr, double* loss_sum,
