@@ -129,7 +129,9 @@ def run_reference(args):
                 warmup=args.warmup, ms_per_step=1e3 * t_tot / max(1, args.steps), higher_is_better=True,
                 scaling="weak", vs_baseline=None, dtype="c128", data="synthetic", impl="reference",
                 config=dict(workload=workload_name(wl), freqs_per_step=n_tot // max(1, args.steps)),
-                cpu_baseline=dict(value=value, unit="evals/s", cores=cores, kind="port", sample=sample),
+                cpu_baseline=dict(value=value, unit="evals/s", cores=cores, kind="port",
+                                  sample=f"{sample} (last of {args.steps} timed steps, each sized by its own "
+                                         f"calibration pass; {n_tot} frequencies in {t_tot:.1f} s in total)"),
                 e2e=dict(value=value, unit="evals/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 gpu_launches=0)
     print(json.dumps(line))
