@@ -40,7 +40,8 @@ enum {
     JPB_OK = 0,
     JPB_EINVAL = 1,    /* bad argument / shape / mode (reference: runtime_error "Invalid `mode`") */
     JPB_ECUDA = 2,     /* CUDA runtime failure */
-    JPB_ESINGULAR = 3, /* a system was numerically singular (reference: UMFPACK status != 0) */
+    JPB_ESINGULAR = 3, /* a system was numerically singular, or its residual failed the
+                          acceptance test (reference: UMFPACK status != 0) */
     JPB_ENOMEM = 4,
     JPB_ESTATE = 5     /* call sequence error (e.g. components not registered) */
 };
@@ -62,6 +63,18 @@ int jpb_set_refinement(jpb_state* st, int steps);
  * need to be meaningful).  No counterpart in the reference (OpenMP over items,
  * InnerState.h:277, is its analogue). */
 int jpb_set_streams(jpb_state* st, int n);
+/* Residual acceptance.  Pivoting is static with partial pivoting inside the 32-wide pivot
+ * tiles only, which is safe for the plate matrices of jax_plate but
+ * not for arbitrary ones, so every system is also judged by its residual:
+ *   jpb_solve      : ||b - A x|| <= tol_final * ||b|| for the solution returned (one more
+ *                    pass over A per call; default 1e-8);
+ *   jpb_eval_*     : the residual of the UNREFINED solution must be <= tol_unrefined * ||b||
+ *                    (default 1e-5; the refinement step that follows squares it), tested on
+ *                    the residual the refinement computes anyway -- no extra pass.
+ * A system that fails gets status bit 2 and the call returns JPB_ESINGULAR.  (UMFPACK's
+ * threshold pivoting has no such restriction; the reference raises only for status != 0,
+ * umfpack_interface.h:11-18.) */
+int jpb_set_residual_tolerance(jpb_state* st, double tol_final, double tol_unrefined);
 
 /* ---- pattern registration (InnerState::add_mat) ------------------------------------
  * indices/indptr: CSC of the N x N pattern; indices_T/indptr_T/perm: the reference's CSR
@@ -89,7 +102,8 @@ int jpb_get_ordering(const jpb_state* st, int solver_num, int32_t* perm);
  *   4: data[B1,nnz]   b[B0,B1,N]   -> out[B0,B1,N]  (B1 factorisations, B0 rhs each)
  * nbatch0 = B (modes 1-3) or B0 (mode 4); nbatch1 = B1 (mode 4 only).
  * transpose != 0 solves A^T x = b (plain transpose, UMFPACK_Aat, InnerState.h:183-185).
- * status (optional, one int per system): 0 ok, 1 singular pivot block encountered. */
+ * status (optional, one int per system): bit 0 (1) zero / non-finite pivot block, bit 1 (2)
+ * relative residual above the tolerance of jpb_set_residual_tolerance. */
 int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const double* data,
               const double* b, int64_t nbatch0, int64_t nbatch1, double* out, int* status);
 int jpb_matvec(jpb_state* st, int solver_num, int mode, int transpose, const double* mat,
@@ -131,6 +145,37 @@ int jpb_eval_loss_grad_dev(jpb_state* st, int solver_num, int64_t B, const doubl
                            const double* rhs_scale, const double* ref, const double* w,
                            int loss_type, int64_t F_total, double* fr, double* loss_sum,
                            double* ct_coef, double* ct_s, int* status, void* stream);
+
+/* Batched parameter candidates (BASELINE configs[4]; jax.vmap over candidates on top of the
+ * vmap over omega, Problem.py:516): the B systems are the flattened (candidate, frequency)
+ * pairs this call owns, cand[b] in [0, ncand) names the candidate of system b, and
+ * loss_sum[c] = sum of the loss terms of candidate c (caller divides by F_total, the sweep
+ * length per candidate).  Everything else as jpb_eval_loss_grad; ct_coef / ct_s stay per
+ * system, so the caller's chain rule yields one gradient per candidate. */
+int jpb_eval_candidates(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                        const double* rhs_scale, const double* ref, const double* w,
+                        int loss_type, int64_t F_total, const int32_t* cand, int ncand,
+                        double* fr, double* loss_sum, double* ct_coef, double* ct_s, int* status);
+int jpb_eval_candidates_dev(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                            const double* rhs_scale, const double* ref, const double* w,
+                            int loss_type, int64_t F_total, const int32_t* cand, int ncand,
+                            double* fr, double* loss_sum, double* ct_coef, double* ct_s,
+                            int* status, void* stream);
+
+/* Gauss-Newton / Levenberg-Marquardt Jacobian rows (BASELINE configs[2]; the model the
+ * reference sketches in Optimizers.py:139-144 and would obtain through mode-4 multi-RHS
+ * sensitivity solves, Sparse.py:267-270 / InnerState.h:289-304).  Same pipeline as
+ * jpb_eval_loss_grad with the cotangent of fr itself, ybar = w * conj(y) / fr:
+ *   ct_coef[b,k] = d fr_b / d coef[b,k],  ct_s[b] = d fr_b / d rhs_scale[b]   (JAX convention)
+ * so that  J[b,p] = d fr_b / d p = Re(sum_k ct_coef[b,k] dcoef[b,k]/dp + ct_s[b] ds[b]/dp).
+ * One factorisation and ONE adjoint solve per frequency give the whole row, where forward
+ * sensitivities need P right-hand sides. */
+int jpb_eval_jacobian(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                      const double* rhs_scale, const double* w, double* fr, double* ct_coef,
+                      double* ct_s, int* status);
+int jpb_eval_jacobian_dev(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                          const double* rhs_scale, const double* w, double* fr, double* ct_coef,
+                          double* ct_s, int* status, void* stream);
 
 /* ---- instrumentation ----------------------------------------------------------------
  * phase timers (ms, CUDA events on the state's stream) of the last jpb_eval_* / jpb_solve

@@ -1,6 +1,8 @@
 """Material models: real parameters -> complex laminate coefficients A_ij, B_ij, D_ij
 (6 each, order 11, 12, 16, 22, 26, 66), mirroring `/root/reference/source/jax_plate/Material.py`
-(`Isotropic` :357-433, `Orthotropic` :436-542, `OrthotropicD4` :545-636, `SOL` :639-788).
+(`Isotropic` :357-433, `Orthotropic` :436-542, `OrthotropicD4` :545-636, `SOL` :639-788,
+`SymmetricalSOL` :791-885).  `tests/test_reference_pin.py` checks every class against values
+produced by the reference's own classes (`tests/golden/ref_transforms.npz`).
 
 The reference writes the transforms in jax.numpy and lets JAX differentiate them; jax is not
 part of this image, so the same formulas are written with torch (complex128) and
@@ -176,6 +178,21 @@ class SOL(Orthotropic):
             Q = torch.stack([E1 / den, nu12 * E2 / den, z, E2 / den, z, G12]).to(_C)
             f = (1 + 1j * beta.to(_C))
             return (MA @ Q) * f, (MB @ Q) * f, (MD @ Q) * f
+        return _transform
+
+
+class SymmetricalSOL(SOL):
+    """SOL whose plies have E1 = E2, `Material.py:791-885`: params (E1, G12, nu12, beta)."""
+    param_names = ("E1", "G12", "nu12", "beta")
+
+    def __init__(self, density, angles, E1=None, G12=None, nu12=None, beta=None):
+        super().__init__(density, angles, E1, E1, G12, nu12, beta)
+
+    def get_ABD_transform(self, h):
+        sol = super().get_ABD_transform(h)
+
+        def _transform(params, *args):
+            return sol(torch.stack([params[0], params[0], params[1], params[2], params[3]]), *args)
         return _transform
 
 

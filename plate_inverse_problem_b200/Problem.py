@@ -10,7 +10,12 @@ ref_fr)`, `.getFRFunction()` -> `f(freqs, params) -> fr[F]`, `.solveForward(freq
   `load_matrices_unsymm` (`pyFFInterface.py:503-509`) -- e.g. from `synthetic.make_plate` --
   instead of an .edp file name;
 * the callable returned by `getLossFunction` also has `.value_and_grad(params)` (the
-  reference obtains it with `jax.value_and_grad`, `Optimizers.py:232,258`);
+  reference obtains it with `jax.value_and_grad`, `Optimizers.py:232,258`); with
+  `params[C, P]` it evaluates C parameter candidates in one batched call (BASELINE
+  configs[4]) and returns `(L[C], g[C, P])`;
+* `getJacobianFunction` / `getGaussNewtonModel` give the residual Jacobian and the
+  Gauss-Newton model `(r^T J / n, J^T J / n)` the reference only sketches
+  (`Optimizers.py:139-144`), one adjoint solve per frequency;
 * with `torch.distributed` initialised the frequency list is sharded over the ranks and the
   loss / gradient partials are summed with ONE all-reduce (NCCL over NVLink).
 """
@@ -54,9 +59,12 @@ def union_pattern_and_align(mats, N: int):
         return m.row.astype(np.int64) + np.int64(N) * m.col.astype(np.int64)
 
     mats = [m.tocoo() for m in mats]
-    pattern = np.array([], dtype=np.int64)
-    for m in mats:
-        pattern = np.union1d(pattern, unwind(m))
+    # the reference folds np.union1d over the 26 key arrays (`Problem.py:320-326`); the sorted
+    # set of unique keys it ends with is one sort + adjacent-difference mask (numpy 2.3's
+    # hash-based unique takes minutes on these structured keys at N ~ 1e5)
+    pattern = np.sort(np.concatenate([unwind(m) for m in mats]))
+    if pattern.size:
+        pattern = pattern[np.concatenate(([True], pattern[1:] != pattern[:-1]))]
     rows, cols = pattern % N, pattern // N
     nz_idx = np.vstack((rows, cols)).T
     sym = symbolic_indices(N, nz_idx)
@@ -179,7 +187,7 @@ class Problem:
         """`Problem.py:933-980`.  Returns `loss(params) -> float` with the extra method
         `loss.value_and_grad(params) -> (float, grad[P])`."""
         frequencies = np.atleast_1d(np.asarray(frequencies, dtype=np.float64))
-        reference_fr = np.asarray(reference_fr, dtype=np.float64)
+        reference_fr = _real_reference(reference_fr)
         assert frequencies.shape[0] == reference_fr.shape[0]
         if func_type not in _lib.LOSS_TYPES:
             raise ValueError(f'Function type "{func_type}" is not supported!')
@@ -189,6 +197,9 @@ class Problem:
 
         def value_and_grad(params):
             p = np.asarray(params, dtype=np.float64) * scaling
+            if p.ndim == 2:
+                L, g = self._candidates_value_and_grad(frequencies, reference_fr, ltype, p)
+                return L, g * scaling
 
             def local(lo, hi):
                 nloc = hi - lo
@@ -215,15 +226,122 @@ class Problem:
 
         def loss(params):
             fr = fr_function(frequencies, np.asarray(params, dtype=np.float64) * scaling)
-            if func_type == "MSE":
-                return float(np.mean(np.abs(fr - reference_fr) ** 2))
-            if func_type == "RMSE":
-                return float(np.mean(np.abs((fr - reference_fr) / reference_fr) ** 2))
-            if func_type == "MSE_AFC":
-                return float(np.mean((np.abs(fr) - np.abs(reference_fr)) ** 2))
-            return float(np.mean((np.log(np.abs(fr)) - np.log(np.abs(reference_fr))) ** 2))
+            return float(np.mean(_residuals(fr, reference_fr, func_type)[0] ** 2))
 
         loss.value_and_grad = value_and_grad
         loss.grad = lambda params: value_and_grad(params)[1]
         loss.__name__ = func_type + "Loss"
         return loss
+
+    # ---- batched parameter candidates (BASELINE configs[4]) --------------------------------
+    def _candidates_value_and_grad(self, frequencies, reference_fr, ltype, cands):
+        """C candidates x F frequencies as ONE flattened batch of C*F systems, sharded
+        contiguously over the ranks; per-candidate loss sums are segmented on the device
+        (`jpb_eval_candidates`), the only exchange is one all-reduce of [C, 1+P]."""
+        C_, P = cands.shape
+        F = frequencies.size
+        lo, hi = parallel.shard_range(C_ * F)
+        acc = np.zeros((C_, 1 + P))
+        if hi > lo:
+            c0, c1 = lo // F, (hi - 1) // F + 1
+            coefs, ss, dcs, dss = [], [], [], []
+            for c in range(c0, c1):
+                coef, s_, dc, ds = self.coefficients(frequencies, cands[c], with_jacobian=True)
+                coefs.append(coef); ss.append(s_); dcs.append(dc); dss.append(ds)
+            sl = slice(lo - c0 * F, hi - c0 * F)
+            coef = np.ascontiguousarray(np.concatenate(coefs)[sl])
+            s_ = np.ascontiguousarray(np.concatenate(ss)[sl])
+            dc, ds = np.concatenate(dcs)[sl], np.concatenate(dss)[sl]
+            n = hi - lo
+            cand = np.ascontiguousarray((np.arange(lo, hi) // F).astype(np.int32))
+            ref = np.ascontiguousarray(np.tile(reference_fr, c1 - c0)[sl])
+            fr, loss_sum = np.zeros(n), np.zeros(C_)
+            ct = np.zeros((n, coef.shape[1]), dtype=np.complex128)
+            cts = np.zeros(n, dtype=np.complex128)
+            st = self._st
+            st.check(st.lib.jpb_eval_candidates(st.h, self.solver_num, n, _lib.ptr(coef), _lib.ptr(s_),
+                                                _lib.ptr(ref), _lib.ptr(self.weights), ltype, F,
+                                                _lib.ptr(cand), C_, _lib.ptr(fr), _lib.ptr(loss_sum),
+                                                _lib.ptr(ct), _lib.ptr(cts), None))
+            g_sys = np.real(np.einsum("fk,fkp->fp", ct, dc) + cts[:, None] * ds)      # [n, P]
+            acc[:, 0] = loss_sum / F
+            np.add.at(acc[:, 1:], cand, g_sys)
+        acc = parallel.allreduce_sum(acc.ravel(), self._st.device).reshape(C_, 1 + P)   # ONE all-reduce
+        return acc[:, 0].copy(), acc[:, 1:].copy()
+
+    # ---- Gauss-Newton / Levenberg-Marquardt model (BASELINE configs[2]) --------------------
+    def getJacobianFunction(self, frequencies):
+        """`jac(params) -> (fr[F], J[F, P])` with `J[f, p] = d fr_f / d p_p`: one numeric
+        factorisation, one forward and ONE adjoint solve per frequency (`jpb_eval_jacobian`);
+        the reference would reach the same matrix through `jax.jacobian` and P-fold batched
+        solves (`_mode=4`, `Sparse.py:267-270`).  Frequencies are sharded over the ranks; every
+        rank receives the full (fr, J)."""
+        frequencies = np.atleast_1d(np.asarray(frequencies, dtype=np.float64))
+        F = frequencies.size
+
+        def jac(params):
+            p = np.asarray(params, dtype=np.float64)
+            lo, hi = parallel.shard_range(F)
+            out = np.zeros((F, 1 + p.size))
+            if hi > lo:
+                n = hi - lo
+                coef, s_, dc, ds = self.coefficients(frequencies[lo:hi], p, with_jacobian=True)
+                coef, s_ = np.ascontiguousarray(coef), np.ascontiguousarray(s_)
+                fr = np.zeros(n)
+                ct = np.zeros((n, coef.shape[1]), dtype=np.complex128)
+                cts = np.zeros(n, dtype=np.complex128)
+                st = self._st
+                st.check(st.lib.jpb_eval_jacobian(st.h, self.solver_num, n, _lib.ptr(coef), _lib.ptr(s_),
+                                                  _lib.ptr(self.weights), _lib.ptr(fr), _lib.ptr(ct),
+                                                  _lib.ptr(cts), None))
+                out[lo:hi, 0] = fr
+                out[lo:hi, 1:] = np.real(np.einsum("fk,fkp->fp", ct, dc) + cts[:, None] * ds)
+            out = parallel.allreduce_sum(out.ravel(), self._st.device).reshape(F, -1)
+            return out[:, 0].copy(), out[:, 1:].copy()
+        return jac
+
+    def getGaussNewtonModel(self, frequencies, reference_fr, func_type: str, scaling_params=None):
+        """The model of `Optimizers.py:139-144` (`get_model_lvmq`): for the loss
+        `mean_f r_f(p)^2` returns `model(x) -> (loss, g = 2 r^T J / n, H = 2 J^T J / n)` with
+        `J = d r / d x` the residual Jacobian in the (scaled) optimisation variables."""
+        frequencies = np.atleast_1d(np.asarray(frequencies, dtype=np.float64))
+        reference_fr = _real_reference(reference_fr)
+        if func_type not in _lib.LOSS_TYPES:
+            raise ValueError(f'Function type "{func_type}" is not supported!')
+        scaling = 1.0 if scaling_params is None else np.array(scaling_params, dtype=np.float64)
+        jac = self.getJacobianFunction(frequencies)
+        n = frequencies.size
+
+        def model(x):
+            fr, J = jac(np.asarray(x, dtype=np.float64) * scaling)
+            r, dr = _residuals(fr, reference_fr, func_type)
+            Jr = (dr[:, None] * J) * scaling
+            return float(np.mean(r ** 2)), 2.0 * (r @ Jr) / n, 2.0 * (Jr.T @ Jr) / n
+        return model
+
+
+def _real_reference(reference_fr):
+    """The reference's losses take `jnp.abs(fr - reference_fr)` and so accept a complex
+    reference FRF (`Problem.py:948-975`); the unsymmetric read-out here is real and the C-ABI
+    takes a real reference, so a genuinely complex one is refused instead of silently losing
+    its imaginary part."""
+    ref = np.asarray(reference_fr)
+    if np.iscomplexobj(ref):
+        if np.any(ref.imag != 0.0):
+            raise ValueError("reference_fr has a non-zero imaginary part: the fused CUDA losses take a real "
+                             "reference FRF (amplitudes); pass np.abs(reference_fr) or the real part")
+        ref = ref.real
+    return np.ascontiguousarray(ref, dtype=np.float64)
+
+
+def _residuals(fr, ref, func_type):
+    """r_f and d r_f / d fr_f of the four losses (`Problem.py:948-975`), loss = mean r^2."""
+    if func_type == "MSE":
+        return fr - ref, np.ones_like(fr)
+    if func_type == "RMSE":
+        return (fr - ref) / ref, 1.0 / ref
+    if func_type == "MSE_AFC":
+        return np.abs(fr) - np.abs(ref), np.sign(fr)
+    if func_type == "MSE_LOG_AFC":
+        return np.log(np.abs(fr)) - np.log(np.abs(ref)), 1.0 / fr
+    raise ValueError(f'Function type "{func_type}" is not supported!')

@@ -170,11 +170,16 @@ def spsolve_vjp(data, x, ct, *, solver_num, transpose=False, state=None):
     return ct_data, ct_b
 
 
-def matvec_vjp_matrix(ct, vec, *, solver_num, transpose=False, state=None):
-    """`_matvec_transpose`, matrix branch (`Sparse.py:172-176`)."""
+def matvec_vjp_matrix(ct, vec, *, solver_num, transpose=False, state=None, as_reference=False):
+    """`_matvec_transpose`, matrix branch (`Sparse.py:172-176`): cotangent of the matrix
+    entries of y = A v, `ct[row] * v[col]`; for y = A^T v rows and columns trade places.
+    The reference's rule ignores `transpose` there and always returns `ct[row] * v[col]`
+    (found by running it, tests/test_reference_pin.py::test_ad_rules_vs_reference); that only
+    matters for second derivatives through transposed solves.  `as_reference=True`
+    reproduces it."""
     st = state or solver_state()
     row, col = st.patterns[solver_num][:, 0], st.patterns[solver_num][:, 1]
-    if transpose:
+    if transpose and not as_reference:
         row, col = col, row
     return ct[..., row] * vec[..., col]
 

@@ -21,10 +21,11 @@ LOSS_TYPES = {"MSE": 0, "RMSE": 1, "MSE_AFC": 2, "MSE_LOG_AFC": 3}
 # every symbol include/jax_plate_b200.h declares
 EXPORTED_SYMBOLS = (
     "jpb_create", "jpb_destroy", "jpb_last_error", "jpb_set_memory_budget", "jpb_set_refinement",
-    "jpb_set_streams",
+    "jpb_set_streams", "jpb_set_residual_tolerance",
     "jpb_add_mat", "jpb_symbolic_info", "jpb_get_ordering", "jpb_solve", "jpb_matvec",
     "jpb_assemble", "jpb_register_components", "jpb_eval_forward", "jpb_eval_loss_grad",
-    "jpb_eval_loss_grad_dev", "jpb_last_timings", "jpb_dmma_peak", "jpb_selftest",
+    "jpb_eval_loss_grad_dev", "jpb_eval_candidates", "jpb_eval_candidates_dev", "jpb_eval_jacobian",
+    "jpb_eval_jacobian_dev", "jpb_last_timings", "jpb_dmma_peak", "jpb_selftest",
     "jpb_host_analyze", "jpb_host_sizes", "jpb_host_export", "jpb_host_free",
 )
 
@@ -60,6 +61,11 @@ def load_library() -> C.CDLL:
     lib.jpb_eval_forward.argtypes = [vp, i32, i64, dp, dp, dp, dp, dp]
     lib.jpb_eval_loss_grad.argtypes = [vp, i32, i64, dp, dp, dp, dp, i32, i64, dp, dp, dp, dp, dp]
     lib.jpb_eval_loss_grad_dev.argtypes = [vp, i32, i64, dp, dp, dp, dp, i32, i64, dp, dp, dp, dp, dp, vp]
+    lib.jpb_eval_candidates.argtypes = [vp, i32, i64, dp, dp, dp, dp, i32, i64, dp, i32, dp, dp, dp, dp, dp]
+    lib.jpb_eval_candidates_dev.argtypes = [vp, i32, i64, dp, dp, dp, dp, i32, i64, dp, i32, dp, dp, dp, dp, dp, vp]
+    lib.jpb_eval_jacobian.argtypes = [vp, i32, i64, dp, dp, dp, dp, dp, dp, dp]
+    lib.jpb_eval_jacobian_dev.argtypes = [vp, i32, i64, dp, dp, dp, dp, dp, dp, dp, vp]
+    lib.jpb_set_residual_tolerance.argtypes = [vp, C.c_double, C.c_double]
     lib.jpb_last_timings.argtypes = [vp, dp]
     lib.jpb_dmma_peak.argtypes = [vp, dp]
     lib.jpb_selftest.argtypes = [vp, dp]

@@ -15,6 +15,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "kernels.cuh"
 #include "symbolic.h"
 
@@ -141,6 +143,8 @@ struct Pattern {
 };
 
 enum Phase { PH_FACTOR = 0, PH_FWD, PH_ADJ, PH_SPMV, PH_GRAD, PH_READOUT, PH_H2D, PH_D2H, PH_COUNT };
+const char* const PHASE_NAMES[PH_COUNT] = {"jpb:factor", "jpb:fwd_solve", "jpb:adj_solve", "jpb:spmv",
+                                           "jpb:grad", "jpb:readout_loss", "jpb:h2d", "jpb:d2h"};
 
 struct TimedSpan {
     int phase;
@@ -156,8 +160,12 @@ struct jpb_state {
     std::string err;
     int64_t budget = 0;
     int refine = 1;
+    // residual acceptance (status bit 2): jpb_solve checks the FINAL residual against
+    // resid_tol; the fused path checks the residual BEFORE the refinement correction against
+    // resid_tol0 (one step squares it) at no extra pass over A
+    double resid_tol = 1e-8, resid_tol0 = 1e-5;
     // workspaces
-    DevBuf F, V, vals, data, vb, vx, vr, vd, vlam, partial, small, hstage, status;
+    DevBuf F, V, vals, data, vb, vx, vr, vd, vlam, partial, small, hstage, status, norms, lterm;
     PinBuf pin;
     // instrumentation
     std::vector<TimedSpan> spans;
@@ -205,6 +213,7 @@ struct Span {
     TimedSpan t;
     bool on;
     Span(jpb_state* st_, cudaStream_t s_, int phase) : st(st_), s(s_), on(st_->timing) {
+        nvtxRangePushA(PHASE_NAMES[phase]);     // NVTX range per phase (host-side enqueue span)
         if (!on) return;
         t.phase = phase;
         t.a = st->ev();
@@ -212,6 +221,7 @@ struct Span {
         cudaEventRecord(t.a, s);
     }
     ~Span() {
+        nvtxRangePop();
         if (!on) return;
         cudaEventRecord(t.b, s);
         st->spans.push_back(t);
@@ -226,6 +236,13 @@ int fail(jpb_state* st, int code, const char* fmt, ...) {
     va_end(ap);
     if (st) st->err = buf;
     return code;
+}
+
+// status bits of a system: 1 = zero / non-finite pivot block, 2 = residual above tolerance
+const char* status_message(int bits) {
+    if (bits & 1) return "matrix is singular (zero pivot block)";
+    return "matrix is singular to working precision or badly scaled for static pivoting: the "
+           "relative residual of a system exceeds the tolerance (jpb_set_residual_tolerance)";
 }
 
 #define JPB_TRY(st) try {
@@ -417,7 +434,7 @@ void tri_solve(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool tran
 // y(b,j) = [rhs(b,j) -] op(A_b) x(b,j)
 void spmv(jpb_state* st, cudaStream_t s, Pattern& P, bool trans, const cd* vals, int64_t vals_sb,
           bool vals_ent_order, const cd* x, int64_t x_sb, int64_t x_sj, const cd* rhs, int64_t rhs_sb,
-          int64_t rhs_sj, cd* y, int nsys, int nrhs) {
+          int64_t rhs_sj, cd* y, int nsys, int nrhs, double* norms = nullptr) {
     Span span(st, s, PH_SPMV);
     const int* ptr = trans ? P.d_csc_ptr : P.d_csr_ptr;
     const int* idx = trans ? P.d_csc_row : P.d_csr_col;
@@ -426,23 +443,40 @@ void spmv(jpb_state* st, cudaStream_t s, Pattern& P, bool trans, const cd* vals,
     dim3 grid((P.S.N + 127) / 128, (unsigned)(nsys * nrhs));
     if ((int64_t)nsys * nrhs > 65535) throw InvalidArg("too many vectors for one spmv launch");
     spmv_kernel<<<grid, 128, 0, s>>>(P.S.N, P.S.nnz, ptr, idx, pos, vals, vals_sb, x, x_sb, x_sj, rhs,
-                                     rhs_sb, rhs_sj, y, nsys);
+                                     rhs_sb, rhs_sj, y, nsys, norms);
     launch_check(st);
 }
 
 // solve + iterative refinement.  x receives the solution in the dense (j*nsys + b) layout.
 void solve_refined(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool trans, const cd* vals,
                    int64_t vals_sb, bool vals_ent_order, const cd* rhs, int64_t rhs_sb, int64_t rhs_sj,
-                   cd* x, cd* V, cd* r, cd* d, int nsys, int nrhs, int phase) {
+                   cd* x, cd* V, cd* r, cd* d, int nsys, int nrhs, int phase, int* status,
+                   bool final_check) {
     VecView vv{rhs, rhs_sb, rhs_sj, x, V, nsys, nrhs};
     tri_solve(st, s, P, F, trans, vv, phase);
+    const int nvec = nsys * nrhs;
+    double* norms = nullptr;
+    if (status && (final_check || st->refine > 0)) norms = (double*)st->norms.get((size_t)nvec * 16);
+    auto flag = [&](double tol) {
+        residual_flag_kernel<<<(nvec + 127) / 128, 128, 0, s>>>(nvec, nsys, norms, tol * tol, status);
+        launch_check(st);
+    };
     for (int it = 0; it < st->refine; ++it) {
-        spmv(st, s, P, trans, vals, vals_sb, vals_ent_order, x, 1, nsys, rhs, rhs_sb, rhs_sj, r, nsys, nrhs);
+        // the residual of the unrefined solution doubles as the acceptance test of the fused path
+        double* nrm = (norms && !final_check && it == 0) ? norms : nullptr;
+        if (nrm) CK(cudaMemsetAsync(nrm, 0, (size_t)nvec * 16, s));
+        spmv(st, s, P, trans, vals, vals_sb, vals_ent_order, x, 1, nsys, rhs, rhs_sb, rhs_sj, r, nsys, nrhs, nrm);
+        if (nrm) flag(st->resid_tol0);
         VecView v2{r, 1, nsys, d, V, nsys, nrhs};
         tri_solve(st, s, P, F, trans, v2, phase);
         int64_t n = (int64_t)nsys * nrhs * P.S.N;
         axpy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, x, d);
         launch_check(st);
+    }
+    if (norms && final_check) {      // ||b - A x|| / ||b|| of what is returned (jpb_solve)
+        CK(cudaMemsetAsync(norms, 0, (size_t)nvec * 16, s));
+        spmv(st, s, P, trans, vals, vals_sb, vals_ent_order, x, 1, nsys, rhs, rhs_sb, rhs_sj, r, nsys, nrhs, norms);
+        flag(st->resid_tol);
     }
 }
 
@@ -477,7 +511,8 @@ void summarise_timings(const jpb_state* st, double* t) {
 // core of the fused evaluation; every pointer is a device pointer
 void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* coef, const cd* scale,
                const double* ref, const double* w, int loss_type, int64_t F_total, cd* u_out, cd* y,
-               double* fr, double* loss_sum, cd* ct_coef, cd* ct_s, int* status, bool adjoint) {
+               double* fr, double* loss_sum, cd* ct_coef, cd* ct_s, int* status, bool adjoint,
+               const int* seg = nullptr, int nseg = 1) {
     if (P.K == 0) throw StateError("components not registered for this pattern (jpb_register_components)");
     const int N = P.S.N;
     const int64_t nnz = P.S.nnz;
@@ -487,6 +522,11 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
     int64_t per = (P.S.front_slots + nnz + P.S.vec_slots + 5 * (int64_t)N) * 16 + nchunks * K * 16 + 256;
     int64_t W = std::max<int64_t>(1, std::min<int64_t>(B, budget_bytes(st) / per));
     W = std::min<int64_t>(W, 65535);
+    {   // equal waves: 250 systems with room for 150 run as 125 + 125, not 150 + 100 (the
+        // narrow launches at the top of the elimination tree cost the same for 100 as for 150)
+        const int64_t nwaves = (B + W - 1) / W;
+        W = std::min<int64_t>(W, (((B + nwaves - 1) / nwaves) + 7) & ~(int64_t)7);
+    }
     st->wave = (double)W;
     cd* F = (cd*)st->F.get((size_t)W * P.S.front_slots * 16);
     cd* vals = (cd*)st->vals.get((size_t)W * nnz * 16);
@@ -497,11 +537,10 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
     cd* vd = (cd*)st->vd.get((size_t)W * N * 16);
     cd* vlam = (cd*)st->vlam.get((size_t)W * N * 16);
     cd* partial = adjoint ? (cd*)st->partial.get((size_t)nchunks * W * K * 16) : nullptr;
-    // small per-wave arrays: ybar [W,R], loss_term [W]
-    char* small = (char*)st->small.get((size_t)W * (R * 16 + 8) + 64);
-    cd* ybar = (cd*)small;
-    double* loss_term = (double*)(small + (size_t)W * R * 16);
-    if (loss_sum) CK(cudaMemsetAsync(loss_sum, 0, sizeof(double), s));
+    // small per-wave array ybar [W,R]; loss terms of the whole batch [B] (summed per segment
+    // = per parameter candidate at the end)
+    cd* ybar = (cd*)st->small.get((size_t)W * R * 16 + 64);
+    double* loss_term = adjoint ? (double*)st->lterm.get((size_t)B * 8) : nullptr;
     if (status) CK(cudaMemsetAsync(status, 0, sizeof(int) * B, s));
 
     // One pipeline (assemble -> factor -> solve -> read-out [-> loss -> adjoint solve -> gradient])
@@ -522,7 +561,8 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
             scale_rhs_kernel<<<grid, 256, 0, sc>>>(N, P.d_rhs_vec, scale + g0, vbc);
             launch_check(st);
         }
-        solve_refined(st, sc, P, Fc, false, valsc, 1, true, vbc, 1, n, vxc, Vc, vrc, vdc, n, 1, PH_FWD);
+        solve_refined(st, sc, P, Fc, false, valsc, 1, true, vbc, 1, n, vxc, Vc, vrc, vdc, n, 1, PH_FWD,
+                      status ? status + g0 : nullptr, false);
         {
             Span span(st, sc, PH_READOUT);
             readout_kernel<<<n, 256, 0, sc>>>(N, R, P.d_Q, vxc, y + g0 * R);
@@ -532,15 +572,16 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
         if (!adjoint) return;
         {
             Span span(st, sc, PH_READOUT);
-            loss_kernel<<<(n + 127) / 128, 128, 0, sc>>>(n, R, y + g0 * R, w, ref + g0, loss_type,
-                                                         1.0 / (double)F_total, fr + g0, loss_term + l0,
-                                                         ybar + l0 * R);
+            loss_kernel<<<(n + 127) / 128, 128, 0, sc>>>(n, R, y + g0 * R, w, ref ? ref + g0 : nullptr,
+                                                         loss_type, 1.0 / (double)F_total, fr + g0,
+                                                         loss_term + g0, ybar + l0 * R);
             launch_check(st);
             dim3 grid((N + 255) / 256, n);
             cotangent_kernel<<<grid, 256, 0, sc>>>(N, R, P.d_Q, ybar + l0 * R, vbc);
             launch_check(st);
         }
-        solve_refined(st, sc, P, Fc, true, valsc, 1, true, vbc, 1, n, vlamc, Vc, vrc, vdc, n, 1, PH_ADJ);
+        solve_refined(st, sc, P, Fc, true, valsc, 1, true, vbc, 1, n, vlamc, Vc, vrc, vdc, n, 1, PH_ADJ,
+                      status ? status + g0 : nullptr, false);
         {
             Span span(st, sc, PH_GRAD);
             const int ngroups = (n + GRAD_SYS - 1) / GRAD_SYS;
@@ -584,10 +625,10 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
                 }
             }
         }
-        if (adjoint) {
-            sum_kernel<<<1, 256, 0, s>>>(nw, loss_term, loss_sum);
-            launch_check(st);
-        }
+    }
+    if (adjoint && loss_sum) {
+        seg_sum_kernel<<<nseg, 256, 0, s>>>((int)B, loss_term, seg, loss_sum);
+        launch_check(st);
     }
 }
 
@@ -622,6 +663,19 @@ int jpb_create(jpb_state** out, int device) {
         set(factor_smem_kernel<true, 128>); set(factor_smem_kernel<false, 128>);
         set(factor_smem_kernel<true, 64>); set(factor_smem_kernel<false, 64>);
         if (!ok) return JPB_ECUDA;
+        // the CTA-per-front solve kernels hold one front-local vector in dynamic shared memory;
+        // the attribute is per function and device, so it is raised once to the cap add_mat
+        // enforces (a later, smaller pattern must not lower it for an earlier one)
+        auto setv = [&](auto kernel) {
+            ok &= cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) == cudaSuccess;
+        };
+        setv(fwd_level_kernel<false, 256>); setv(fwd_level_kernel<true, 256>);
+        setv(bwd_level_kernel<false, 256>); setv(bwd_level_kernel<true, 256>);
+        setv(fwd_level_kernel<false, 128>); setv(fwd_level_kernel<true, 128>);
+        setv(bwd_level_kernel<false, 128>); setv(bwd_level_kernel<true, 128>);
+        setv(fwd_level_kernel<false, 64>); setv(fwd_level_kernel<true, 64>);
+        setv(bwd_level_kernel<false, 64>); setv(bwd_level_kernel<true, 64>);
+        if (!ok) return JPB_ECUDA;
     }
     *out = st.release();
     return JPB_OK;
@@ -651,6 +705,14 @@ int jpb_set_streams(jpb_state* st, int n) {
 int jpb_set_refinement(jpb_state* st, int steps) {
     if (!st || steps < 0 || steps > 8) return fail(st, JPB_EINVAL, "refinement steps must be in [0, 8]");
     st->refine = steps;
+    return JPB_OK;
+}
+
+int jpb_set_residual_tolerance(jpb_state* st, double tol_final, double tol_unrefined) {
+    if (!st || !(tol_final > 0.0) || !(tol_unrefined > 0.0))
+        return fail(st, JPB_EINVAL, "residual tolerances must be positive");
+    st->resid_tol = tol_final;
+    st->resid_tol0 = tol_unrefined;
     return JPB_OK;
 }
 
@@ -830,17 +892,6 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
     // the dynamic shared memory of the solve kernels holds one front-local vector
     size_t smem = (size_t)S.max_s * sizeof(cd);
     if (smem > 200 * 1024) throw InvalidArg("add_mat: largest front exceeds the solve kernels' shared memory");
-    if (smem > 40 * 1024) {
-        auto set = [&](auto kernel) {
-            CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        };
-        set(fwd_level_kernel<false, 256>); set(fwd_level_kernel<true, 256>);
-        set(bwd_level_kernel<false, 256>); set(bwd_level_kernel<true, 256>);
-        set(fwd_level_kernel<false, 128>); set(fwd_level_kernel<true, 128>);
-        set(bwd_level_kernel<false, 128>); set(bwd_level_kernel<true, 128>);
-        set(fwd_level_kernel<false, 64>); set(fwd_level_kernel<true, 64>);
-        set(bwd_level_kernel<false, 64>); set(bwd_level_kernel<true, 64>);
-    }
     st->pats.push_back(std::move(P));
     if (solver_num) *solver_num = (int)st->pats.size() - 1;
     return JPB_OK;
@@ -926,7 +977,7 @@ int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const doub
                 }
             }
             solve_refined(st, s, P, F, trans, dat, 1, false, vb, sb, sj, vx, V, vr, vd, nw, nj,
-                          trans ? PH_ADJ : PH_FWD);
+                          trans ? PH_ADJ : PH_FWD, dstat + i0, true);
             {
                 Span span(st, s, PH_D2H);
                 for (int j = 0; j < nj; ++j)
@@ -943,7 +994,7 @@ int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const doub
         if (status) status[i] = hstat[i];
         bad |= hstat[i];
     }
-    if (bad) return fail(st, JPB_ESINGULAR, "solve: matrix is singular (zero pivot block)");
+    if (bad) return fail(st, JPB_ESINGULAR, "solve: %s", status_message(bad));
     return JPB_OK;
     JPB_CATCH(st)
 }
@@ -1089,74 +1140,72 @@ int jpb_eval_forward(jpb_state* st, int solver_num, int64_t B, const double* coe
         if (status) status[i] = hstat[i];
         bad |= hstat[i];
     }
-    if (bad) return fail(st, JPB_ESINGULAR, "eval_forward: a system is singular (zero pivot block)");
+    if (bad) return fail(st, JPB_ESINGULAR, "eval_forward: %s", status_message(bad));
     return JPB_OK;
     JPB_CATCH(st)
 }
 
-int jpb_eval_loss_grad_dev(jpb_state* st, int solver_num, int64_t B, const double* coef,
-                           const double* rhs_scale, const double* ref, const double* w, int loss_type,
-                           int64_t F_total, double* fr, double* loss_sum, double* ct_coef, double* ct_s,
-                           int* status, void* stream) {
-    JPB_TRY(st)
-    Pattern& P = pattern(st, solver_num);
-    if (!coef || !rhs_scale || !ref || !w || !fr || !loss_sum || !ct_coef || !ct_s || B <= 0 || F_total < B)
-        throw InvalidArg("eval_loss_grad: bad arguments");
-    if (loss_type < 0 || loss_type > 3) throw InvalidArg("eval_loss_grad: unknown loss type");
-    CK(cudaSetDevice(st->device));
-    st->reset_timing();
-    cudaStream_t s = (cudaStream_t)stream;
-    cd* dy = (cd*)st->hstage.get((size_t)B * P.R * 16 + 64);
-    eval_core(st, s, P, B, (const cd*)coef, (const cd*)rhs_scale, ref, w, loss_type, F_total, nullptr, dy,
-              fr, loss_sum, (cd*)ct_coef, (cd*)ct_s, status, true);
-    return JPB_OK;
-    JPB_CATCH(st)
-}
+namespace {
 
-int jpb_eval_loss_grad(jpb_state* st, int solver_num, int64_t B, const double* coef,
-                       const double* rhs_scale, const double* ref, const double* w, int loss_type,
-                       int64_t F_total, double* fr, double* loss_sum, double* ct_coef, double* ct_s,
-                       int* status) {
-    JPB_TRY(st)
-    Pattern& P = pattern(st, solver_num);
-    if (!coef || !rhs_scale || !ref || !w || !fr || !loss_sum || !ct_coef || !ct_s || B <= 0 || F_total < B)
+void check_eval_args(Pattern& P, int64_t B, const void* coef, const void* rhs_scale, const void* ref,
+                     const void* w, int loss_type, int64_t F_total, const void* fr, const void* loss_sum,
+                     const void* ct_coef, const void* ct_s, const int* seg, int nseg) {
+    if (!coef || !rhs_scale || !w || !fr || !ct_coef || !ct_s || B <= 0)
         throw InvalidArg("eval_loss_grad: bad arguments");
-    if (loss_type < 0 || loss_type > 3) throw InvalidArg("eval_loss_grad: unknown loss type");
+    if (loss_type < 0 || loss_type > 4) throw InvalidArg("eval_loss_grad: unknown loss type");
+    if (loss_type != 4 && (!ref || !loss_sum || F_total < 1)) throw InvalidArg("eval_loss_grad: bad arguments");
+    if (nseg < 1 || (nseg > 1 && !seg)) throw InvalidArg("eval_loss_grad: bad candidate segments");
+    if (B > INT32_MAX) throw InvalidArg("eval_loss_grad: batch too large");
     if (P.K == 0) throw StateError("components not registered for this pattern (jpb_register_components)");
+}
+
+// host-buffer evaluation: inputs are packed into the page-locked mirror and go to the device in
+// one asynchronous copy, results come back the same way
+int eval_host(jpb_state* st, int solver_num, int64_t B, const double* coef, const double* rhs_scale,
+              const double* ref, const double* w, int loss_type, int64_t F_total, const int32_t* seg,
+              int nseg, double* fr, double* loss_sum, double* ct_coef, double* ct_s, int* status) {
+    JPB_TRY(st)
+    Pattern& P = pattern(st, solver_num);
+    check_eval_args(P, B, coef, rhs_scale, ref, w, loss_type, F_total, fr, loss_sum, ct_coef, ct_s, seg, nseg);
+    if (seg)
+        for (int64_t i = 0; i < B; ++i)
+            if (seg[i] < 0 || seg[i] >= nseg) throw InvalidArg("eval_candidates: candidate id out of range");
     CK(cudaSetDevice(st->device));
     st->reset_timing();
     cudaStream_t s = st->stream;
     const int K = P.K, R = P.R;
     // device staging block, inputs first and results last so that each direction is one copy:
-    //   in : coef [B,K] c, scale [B] c, ref [B] d, w [4] d
+    //   in : coef [B,K] c, scale [B] c, ref [B] d, w [4] d, seg [B] i
     //   -- : y [B,R] c (device only)
-    //   out: ct_coef [B,K] c, ct_s [B] c, fr [B] d, loss [2] d, status [B] i
-    const size_t in_bytes = ((size_t)B * (K * 16 + 16 + 8) + 32 + 15) & ~(size_t)15;
+    //   out: ct_coef [B,K] c, ct_s [B] c, fr [B] d, loss [nseg] d, status [B] i
+    const size_t in_bytes = ((size_t)B * (K * 16 + 16 + 8 + 4) + 32 + 15) & ~(size_t)15;
     const size_t y_bytes = (size_t)B * R * 16;
-    const size_t out_bytes = (size_t)B * (K * 16 + 16 + 8 + 4) + 16;
+    const size_t out_bytes = (size_t)B * (K * 16 + 16 + 8 + 4) + (size_t)nseg * 8 + 16;
     char* stage = (char*)st->hstage.get(in_bytes + y_bytes + out_bytes + 64);
     char* pin = (char*)st->pin.get(in_bytes + out_bytes);
     cd* dcoef = (cd*)stage;
     cd* dscale = dcoef + B * K;
     double* dref = (double*)(dscale + B);
     double* dw = dref + B;
+    int* dseg = (int*)(dw + 4);
     cd* dy = (cd*)(stage + in_bytes);
     char* dout = stage + in_bytes + y_bytes;
     cd* dct = (cd*)dout;
     cd* dcts = dct + B * K;
     double* dfr = (double*)(dcts + B);
     double* dloss = dfr + B;
-    int* dstat = (int*)(dloss + 2);
+    int* dstat = (int*)(dloss + nseg);
     {
         Span span(st, s, PH_H2D);
         memcpy(pin, coef, (size_t)B * K * 16);
         memcpy(pin + ((char*)dscale - stage), rhs_scale, (size_t)B * 16);
-        memcpy(pin + ((char*)dref - stage), ref, (size_t)B * 8);
+        if (ref) memcpy(pin + ((char*)dref - stage), ref, (size_t)B * 8);
         memcpy(pin + ((char*)dw - stage), w, (size_t)R * 8);
+        if (seg) memcpy(pin + ((char*)dseg - stage), seg, (size_t)B * 4);
         CK(cudaMemcpyAsync(stage, pin, in_bytes, cudaMemcpyHostToDevice, s));
     }
-    eval_core(st, s, P, B, dcoef, dscale, dref, dw, loss_type, F_total, nullptr, dy, dfr, dloss, dct, dcts,
-              dstat, true);
+    eval_core(st, s, P, B, dcoef, dscale, ref ? dref : nullptr, dw, loss_type, std::max<int64_t>(F_total, 1),
+              nullptr, dy, dfr, dloss, dct, dcts, dstat, true, seg ? dseg : nullptr, nseg);
     char* pout = pin + in_bytes;
     {
         Span span(st, s, PH_D2H);
@@ -1166,16 +1215,78 @@ int jpb_eval_loss_grad(jpb_state* st, int solver_num, int64_t B, const double* c
     memcpy(ct_coef, pout, (size_t)B * K * 16);
     memcpy(ct_s, pout + ((char*)dcts - dout), (size_t)B * 16);
     memcpy(fr, pout + ((char*)dfr - dout), (size_t)B * 8);
-    memcpy(loss_sum, pout + ((char*)dloss - dout), 8);
+    if (loss_sum) memcpy(loss_sum, pout + ((char*)dloss - dout), (size_t)nseg * 8);
     const int* hstat = (const int*)(pout + ((char*)dstat - dout));
     int bad = 0;
     for (int64_t i = 0; i < B; ++i) {
         if (status) status[i] = hstat[i];
         bad |= hstat[i];
     }
-    if (bad) return fail(st, JPB_ESINGULAR, "eval_loss_grad: a system is singular (zero pivot block)");
+    if (bad) return fail(st, JPB_ESINGULAR, "%s", status_message(bad));
     return JPB_OK;
     JPB_CATCH(st)
+}
+
+}  // namespace
+
+int jpb_eval_candidates_dev(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                            const double* rhs_scale, const double* ref, const double* w, int loss_type,
+                            int64_t F_total, const int32_t* cand, int ncand, double* fr, double* loss_sum,
+                            double* ct_coef, double* ct_s, int* status, void* stream) {
+    JPB_TRY(st)
+    Pattern& P = pattern(st, solver_num);
+    check_eval_args(P, B, coef, rhs_scale, ref, w, loss_type, F_total, fr, loss_sum, ct_coef, ct_s, cand, ncand);
+    CK(cudaSetDevice(st->device));
+    st->reset_timing();
+    cudaStream_t s = (cudaStream_t)stream;
+    cd* dy = (cd*)st->hstage.get((size_t)B * P.R * 16 + 64);
+    eval_core(st, s, P, B, (const cd*)coef, (const cd*)rhs_scale, ref, w, loss_type, std::max<int64_t>(F_total, 1),
+              nullptr, dy, fr, loss_sum, (cd*)ct_coef, (cd*)ct_s, status, true, cand, ncand);
+    return JPB_OK;
+    JPB_CATCH(st)
+}
+
+int jpb_eval_loss_grad_dev(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                           const double* rhs_scale, const double* ref, const double* w, int loss_type,
+                           int64_t F_total, double* fr, double* loss_sum, double* ct_coef, double* ct_s,
+                           int* status, void* stream) {
+    if (loss_type == 4) return fail(st, JPB_EINVAL, "eval_loss_grad: unknown loss type");
+    return jpb_eval_candidates_dev(st, solver_num, B, coef, rhs_scale, ref, w, loss_type, F_total, nullptr, 1,
+                                   fr, loss_sum, ct_coef, ct_s, status, stream);
+}
+
+int jpb_eval_loss_grad(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                       const double* rhs_scale, const double* ref, const double* w, int loss_type,
+                       int64_t F_total, double* fr, double* loss_sum, double* ct_coef, double* ct_s,
+                       int* status) {
+    if (loss_type == 4) return fail(st, JPB_EINVAL, "eval_loss_grad: unknown loss type");
+    if (F_total < B) return fail(st, JPB_EINVAL, "eval_loss_grad: bad arguments");
+    return eval_host(st, solver_num, B, coef, rhs_scale, ref, w, loss_type, F_total, nullptr, 1, fr, loss_sum,
+                     ct_coef, ct_s, status);
+}
+
+int jpb_eval_candidates(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                        const double* rhs_scale, const double* ref, const double* w, int loss_type,
+                        int64_t F_total, const int32_t* cand, int ncand, double* fr, double* loss_sum,
+                        double* ct_coef, double* ct_s, int* status) {
+    if (loss_type == 4) return fail(st, JPB_EINVAL, "eval_candidates: unknown loss type");
+    if (!cand) return fail(st, JPB_EINVAL, "eval_candidates: null candidate ids");
+    return eval_host(st, solver_num, B, coef, rhs_scale, ref, w, loss_type, F_total, cand, ncand, fr, loss_sum,
+                     ct_coef, ct_s, status);
+}
+
+int jpb_eval_jacobian(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                      const double* rhs_scale, const double* w, double* fr, double* ct_coef, double* ct_s,
+                      int* status) {
+    return eval_host(st, solver_num, B, coef, rhs_scale, nullptr, w, 4, 1, nullptr, 1, fr, nullptr, ct_coef,
+                     ct_s, status);
+}
+
+int jpb_eval_jacobian_dev(jpb_state* st, int solver_num, int64_t B, const double* coef,
+                          const double* rhs_scale, const double* w, double* fr, double* ct_coef,
+                          double* ct_s, int* status, void* stream) {
+    return jpb_eval_candidates_dev(st, solver_num, B, coef, rhs_scale, nullptr, w, 4, 1, nullptr, 1, fr,
+                                   nullptr, ct_coef, ct_s, status, stream);
 }
 
 int jpb_last_timings(const jpb_state* st, double* t10) {

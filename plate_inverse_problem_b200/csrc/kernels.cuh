@@ -1343,10 +1343,11 @@ __global__ void spmv_kernel(int N, int64_t nnz, const int* __restrict__ ptr,
                             const cd* __restrict__ vals, int64_t vals_sb,
                             const cd* __restrict__ x, int64_t x_sb, int64_t x_sj,
                             const cd* __restrict__ rhs, int64_t rhs_sb, int64_t rhs_sj,
-                            cd* y, int nsys) {
+                            cd* y, int nsys, double* norms) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= N) return;
     const int b = blockIdx.y % nsys, j = blockIdx.y / nsys;
+    double nr = 0.0, nb2 = 0.0;     // |r_i|^2 and |rhs_i|^2 of this row (residual check)
+    if (i < N) {
     const cd* vb = vals + (int64_t)b * vals_sb * nnz;
     const cd* xb = x + ((int64_t)j * x_sj + (int64_t)b * x_sb) * N;
     cd acc = make_double2(0.0, 0.0);
@@ -1383,8 +1384,46 @@ __global__ void spmv_kernel(int N, int64_t nnz, const int* __restrict__ ptr,
         cd r = rhs[((int64_t)j * rhs_sj + (int64_t)b * rhs_sb) * N + i];
         acc.x = r.x - acc.x;
         acc.y = r.y - acc.y;
+        nr = acc.x * acc.x + acc.y * acc.y;
+        nb2 = r.x * r.x + r.y * r.y;
     }
     yb[i] = acc;
+    }
+    // norms[(j * nsys + b) * 2 + {0, 1}] += sum_i {|r_i|^2, |rhs_i|^2}: feeds the per-system
+    // residual check (status bit 2); the summation order is irrelevant for a threshold test
+    if (norms) {
+        __shared__ double red[2][32];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            nr += __shfl_xor_sync(0xffffffffu, nr, o);
+            nb2 += __shfl_xor_sync(0xffffffffu, nb2, o);
+        }
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        if (lane == 0) { red[0][warp] = nr; red[1][warp] = nb2; }
+        __syncthreads();
+        if (warp == 0) {
+            const int nw = blockDim.x >> 5;
+            double a = lane < nw ? red[0][lane] : 0.0, c = lane < nw ? red[1][lane] : 0.0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                a += __shfl_xor_sync(0xffffffffu, a, o);
+                c += __shfl_xor_sync(0xffffffffu, c, o);
+            }
+            if (lane == 0) {
+                atomicAdd(norms + 2 * (int64_t)blockIdx.y, a);
+                atomicAdd(norms + 2 * (int64_t)blockIdx.y + 1, c);
+            }
+        }
+    }
+}
+
+// status[vec % nsys] |= 2 where ||r||^2 > tol2 * ||rhs||^2 (or the residual is not finite)
+__global__ void residual_flag_kernel(int nvec, int nsys, const double* __restrict__ norms, double tol2,
+                                     int* status) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nvec) return;
+    const double nr = norms[2 * v], nb = norms[2 * v + 1];
+    if (!(nr <= tol2 * nb) && !(nr == 0.0)) atomicOr(status + v % nsys, 2);
 }
 
 // x += d
@@ -1472,9 +1511,11 @@ __global__ void loss_kernel(int B, int R, const cd* __restrict__ y, const double
         cd v = y[(int64_t)b * R + r];
         s2 += w[r] * (v.x * v.x + v.y * v.y);
     }
-    const double f = sqrt(s2), rf = ref[b];
+    const double f = sqrt(s2), rf = ref ? ref[b] : 1.0;
     double term, dfr;
-    if (loss_type == 0) {            // MSE
+    if (loss_type == 4) {            // identity: the cotangent of fr itself (Jacobian rows)
+        term = f; dfr = 1.0; inv_F = 1.0;
+    } else if (loss_type == 0) {     // MSE
         term = (f - rf) * (f - rf); dfr = 2.0 * (f - rf);
     } else if (loss_type == 1) {     // RMSE
         double q = (f - rf) / rf; term = q * q; dfr = 2.0 * (f - rf) / (rf * rf);
@@ -1598,6 +1639,24 @@ __global__ void grad_reduce_kernel(int nchunks, int64_t nbk, const cd* __restric
     cd v = make_double2(0.0, 0.0);
     for (int c = 0; c < nchunks; ++c) { cd p = partial[(int64_t)c * nbk + i]; v.x += p.x; v.y += p.y; }
     out[i] = v;
+}
+
+// out[g] = sum of v[b] over the systems with seg[b] == g (seg == nullptr: one segment);
+// one CTA per segment, fixed order => deterministic
+__global__ void seg_sum_kernel(int n, const double* __restrict__ v, const int* __restrict__ seg, double* out) {
+    __shared__ double red[32];
+    const int g = blockIdx.x;
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x)
+        if (!seg || seg[i] == g) acc += v[i];
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        double a = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.0;
+        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+        if (threadIdx.x == 0) out[g] = a;
+    }
 }
 
 // sum of a double vector by one CTA (fixed order)
