@@ -3,12 +3,18 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload cfg1]
 
-One "step" = one loss/gradient evaluation over a frequency sweep (BASELINE.json configs[1]:
-~2e4-DOF composite plate, 400 frequencies per GPU; weak scaling: N GPUs -> 400*N
-frequencies, sharded contiguously, ONE all-reduce of [loss, grad] per step).
-Prints one JSON line (see the task contract); `--impl reference` times the reference's CPU
-algorithm (oracle port: SuperLU stand-in for UMFPACK, two numeric LUs per frequency, one
-process per host core) on a bounded sample of the same workload.
+One "step" = one loss/gradient evaluation over a frequency sweep.  The line's headline
+(`value`, `e2e`, `roofline`, `cpu_baseline`, `parity`) is BASELINE.json configs[1]: ~2e4-DOF
+composite plate, 400 frequencies per GPU, weak scaling (N GPUs -> 400*N frequencies, sharded
+contiguously, ONE all-reduce of [loss, grad] per step).  The same line carries a second,
+independently timed object `north_star`: configs[3], the ~1e5-DOF plate with a FIXED sweep of
+2000 frequencies split over the N GPUs (strong scaling; at N = 1 with its own CPU arm), which
+is the configuration the north-star targets (>= 50x the host cores on 1 GPU, >= 85 % strong
+scaling at 8) are quoted on.  `--workload X --scaling strong|weak --freqs F` re-targets the
+headline; `--no-north-star` skips the second object.
+`--impl reference` times the reference's CPU algorithm (oracle port: SuperLU stand-in for
+UMFPACK, two numeric LUs per frequency, one process per host core) on a bounded sample of
+the same workload.
 """
 import argparse
 import json
@@ -35,10 +41,13 @@ PARAMS = np.array([130e9, 9e9, 5e9, 0.3, 0.01])
 ANGLES = (0, 45, -45, 90)
 E2E_WARMUP = 8
 FREQS_PER_GPU = {"cfg1": 400, "cfg0": 400, "small": 64, "cfg4": 96, "cfg5": 160, "40k": 256}
+NORTH_STAR = ("cfg4", 2000)        # BASELINE.json configs[3]: fixed sweep, split over the GPUs
 METRIC = "freq-point forward+adjoint+grad evals/s"
-# DRAM bytes moved by the factor launches of one wave, from the committed ncu launch list
-# (profiles/r1o_launches_cfg1_F400.csv: 40.4 + 4.9 GB read, 36.6 + 9.7 GB written)
-FACTOR_DRAM_BYTES = {("cfg1", 400): 91.6e9}
+# nnz(L+U) of a CPU sparse LU of the same matrix, measured in this container (SURVEY 8d guard:
+# the algorithmic bytes of the roofline use min(ours, this)): cfg1 SuperLU MMD_AT_PLUS_A in
+# symmetric mode; 40k / cfg4 SuperLU on the nested-dissection ordering (MMD does not finish)
+CPU_FILL = {"cfg1": 2270753, "40k": 6730240, "cfg4": 19848412}
+ND_ORACLE_ABOVE = 30000            # N above which the CPU arm factors P A P^T (ND ordering)
 
 
 def make_inputs(workload):
@@ -56,8 +65,13 @@ def _cpu_init(workload):
     from plate_inverse_problem_b200.Problem import AP1030
     plate = make_inputs(workload)
     inertia = orc.inertia_scalars(H, RHO, AP1030.mass, AP1030.radius, AP1030.height)
-    _ORC["op"] = orc.OracleProblem(plate, orc.make_transform("sol", H, ANGLES), inertia, AP1030.height,
-                                   AP1030.effective_height, AP1030.transverse_sensitivity)
+    _ORC["op"] = op = orc.OracleProblem(plate, orc.make_transform("sol", H, ANGLES), inertia, AP1030.height,
+                                        AP1030.effective_height, AP1030.transverse_sensitivity)
+    if plate.N > ND_ORACLE_ABOVE:
+        # SuperLU's MMD ordering does not finish at N ~ 1e5: factor P A P^T with the nested-dissection
+        # ordering of the symbolic phase (host-only entry point of the library; no GPU involved)
+        from plate_inverse_problem_b200 import _lib
+        op.ordering = _lib.host_symbolic(plate.N, op.native["indices"], op.native["indptr"])["perm"]
     _ORC["orc"] = orc
 
 
@@ -76,6 +90,15 @@ def _cpu_eval(args):
     return L, g
 
 
+def _solver_note(workload):
+    from plate_inverse_problem_b200.synthetic import NAMED_SIZES
+    nx, ny = NAMED_SIZES[workload]
+    big = 3 * (nx + 1) * (ny + 1) + 3 * nx * ny > ND_ORACLE_ABOVE      # ~N
+    return ("scipy SuperLU on the nested-dissection ordering, diagonal pivot threshold 1e-5 (MMD does not "
+            "finish at this size; 1e-3 triples the fill and costs 26 s per factorisation)" if big else
+            "scipy SuperLU MMD_AT_PLUS_A, symmetric mode, diagonal pivot threshold 1e-3")
+
+
 def cpu_baseline(workload, target_seconds=15.0, cores=None, repeats=1):
     import multiprocessing as mp
     cores = cores or os.cpu_count()
@@ -91,8 +114,8 @@ def cpu_baseline(workload, target_seconds=15.0, cores=None, repeats=1):
         if t1 > target_seconds:      # the calibration pass already is the bounded sample
             return dict(value=cores / t1, unit="evals/s", cores=cores, kind="port",
                         sample=f"{cores} frequencies of the {workload} sweep, 2 numeric LU + 2 solves "
-                               f"each (scipy SuperLU stand-in for UMFPACK: UMFPACK unavailable on this "
-                               f"box), one process per core, {t1:.1f} s"), cores, t1
+                               f"each ({_solver_note(workload)}; stand-in for UMFPACK, which is unavailable on "
+                               f"this box), one process per core, {t1:.1f} s"), cores, t1
         n = per_core * cores
         freqs = np.linspace(40.0, 600.0, n)
         best = None
@@ -103,7 +126,7 @@ def cpu_baseline(workload, target_seconds=15.0, cores=None, repeats=1):
             best = dt if best is None else min(best, dt)
     return dict(value=n / best, unit="evals/s", cores=cores, kind="port",
                 sample=f"{n} frequencies of the {workload} sweep, 2 numeric LU + 2 solves each "
-                       f"(scipy SuperLU stand-in for UMFPACK: UMFPACK unavailable on this box), "
+                       f"({_solver_note(workload)}; stand-in for UMFPACK, which is unavailable on this box), "
                        f"one process per core, {best:.1f} s"), n, best
 
 
@@ -224,12 +247,175 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------------- GPU
+def committed_factor_traffic(wl, nsys):
+    """dram__bytes_read + write of the factor launches of one step, from the committed ncu launch
+    list of this workload (profiles/r2_launches_<wl>_F<nsys>.csv), or None."""
+    import csv
+    import glob
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", f"r2*_launches_{wl}_F{nsys}.csv")), reverse=True):
+        rows = list(csv.DictReader(l for l in open(path) if not l.startswith("==")))
+        if not rows or "dram__bytes_read.sum" not in {r["Metric Name"] for r in rows}:
+            continue
+        ids = [r["ID"] for r in rows if "assemble_kernel" in r["Kernel Name"]]
+        start = int(ids[-1]) if ids else 0
+        tot = sum(float(r["Metric Value"]) for r in rows
+                  if int(r["ID"]) >= start and "factor" in r["Kernel Name"] and r["Metric Name"].startswith("dram__bytes"))
+        return tot, os.path.relpath(path, ROOT)
+    return None, None
+
+
+def whole_step_roofline(info, K, nsys, refine, hbm_gbs, dmma_tf, t_step_ms, wl):
+    """T_bound = bytes / BW_HBM + flops / FP64 peak per evaluation (phases are
+    sequential), fraction = T_bound / T_measured.  nnz(L+U) is guarded by the CPU LU's fill."""
+    N, nnz = info["N"], info["nnz"]
+    nnz_lu = min(info["nnz_lu"], CPU_FILL.get(wl, info["nnz_lu"]))
+    wave = max(1.0, min(nsys, 400.0))
+    by = dict(assembly=16 * nnz + K * 8 * nnz / wave, factor_write=16 * nnz_lu, fwd_solve=16 * nnz_lu,
+              adj_solve=16 * nnz_lu, refinement_spmv=2 * refine * 16 * nnz,
+              gradient=K * 8 * nnz / wave + 2 * 16 * N + 8 * nnz / wave, vectors=6 * 16 * N)
+    tot = sum(by.values())
+    t_bound = tot / (hbm_gbs * 1e9) + info["flops"] / (dmma_tf * 1e12)
+    t_meas = t_step_ms * 1e-3 / nsys
+    return dict(t_bound_us=t_bound * 1e6, t_measured_us=t_meas * 1e6, frac=t_bound / t_meas,
+                bytes_per_system=tot, flops_per_system=info["flops"], nnz_lu_used=nnz_lu,
+                nnz_lu_ours=info["nnz_lu"], peaks=dict(hbm_gbs=hbm_gbs, fp64_dmma_tflops=dmma_tf),
+                note="bytes use min(nnz(L+U) of this ordering incl. amalgamation zeros, CPU-LU fill of the same "
+                     "matrix); flops are those of this repository's own schedule (symbolic phase)")
+
+
+def parity_sample(prob, plate, wl, freqs, ref_fr, nsamp):
+    """Errors of the timed workload against the oracle on a bounded sample of its frequencies
+    (always including the ones next to the 100 Hz resonance, where cond(A) peaks)."""
+    from oracle import jax_plate_oracle as orc
+    from plate_inverse_problem_b200.Problem import AP1030
+    from plate_inverse_problem_b200 import _lib
+    inertia = orc.inertia_scalars(H, RHO, AP1030.mass, AP1030.radius, AP1030.height)
+    op = orc.OracleProblem(plate, orc.make_transform("sol", H, ANGLES), inertia, AP1030.height,
+                           AP1030.effective_height, AP1030.transverse_sensitivity)
+    if plate.N > ND_ORACLE_ABOVE:
+        op.ordering = _lib.host_symbolic(plate.N, op.native["indices"], op.native["indptr"])["perm"]
+    near = np.argsort(np.abs(freqs - 100.35))[:2]
+    idx = np.unique(np.concatenate([near, np.linspace(0, freqs.size - 1, max(1, nsamp - 2)).astype(int)]))
+    fs, rs = freqs[idx], ref_fr[idx]
+    fr, y, u = prob._forward_raw(fs, PARAMS, return_u=True)
+    L, g = prob.getLossFunction(fs, rs, "MSE_LOG_AFC").value_and_grad(PARAMS)
+    L_o, g_o, aux = op.loss_and_grad(fs, PARAMS, rs, "MSE_LOG_AFC", reuse_factor=True)
+    rel = lambda a, b: float(np.max(np.abs(a - b)) / np.max(np.abs(b)))
+    return dict(u_rel=max(rel(u[i], aux["U"][i]) for i in range(fs.size)),
+                fr_rel=float(np.max(np.abs(fr - aux["fr"]) / np.abs(aux["fr"]))),
+                loss_rel=float(abs(L - L_o) / abs(L_o)), grad_rel=rel(g, g_o), vs="SuperLU stand-in (oracle)",
+                sample=f"{fs.size} of the {freqs.size} frequencies of the timed sweep incl. the two nearest to "
+                       f"100.35 Hz; u_rel is the max over them of max|u - u_oracle| / max|u_oracle| (both "
+                       f"solvers carry cond(A)*eps there), fr/loss/grad as in north_star")
+
+
+class Arm:
+    """One workload on this rank's GPU: problem, device-resident inputs, the two timed arms."""
+
+    def __init__(self, wl, F_total, world, rank, local, dev):
+        import torch
+        from plate_inverse_problem_b200 import _lib
+        from plate_inverse_problem_b200.Material import SOL
+        from plate_inverse_problem_b200.Problem import AP1030, Geometry, Problem
+        self.wl, self.F_total, self.world, self.rank, self.dev = wl, F_total, world, rank, dev
+        self.plate = make_inputs(wl)
+        self.prob = prob = Problem(Geometry(H, self.plate), SOL(RHO, ANGLES, *PARAMS), AP1030, device=local)
+        self.st = prob._st
+        self.info = prob.symbolic_info()
+        self.freqs = np.linspace(40.0, 600.0, F_total)
+        pert = PARAMS * np.array([1.1, 1.1, 1.2, 1.0, 1.5])      # cpu_benchmark.py:30 style reference FRF
+        self.ref_fr = prob.solveForward(self.freqs, pert)
+        self.loss = prob.getLossFunction(self.freqs, self.ref_fr, "MSE_LOG_AFC")
+        lo, hi = (F_total * rank) // world, (F_total * (rank + 1)) // world
+        coef, s, dc, ds = prob.coefficients(self.freqs[lo:hi], PARAMS, with_jacobian=True)
+        self.nloc, self.K = hi - lo, coef.shape[1]
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+        self.d = dict(coef=t(coef), s=t(s), ref=t(self.ref_fr[lo:hi]), w=t(prob.weights), dc=t(dc), ds=t(ds),
+                      fr=torch.zeros(self.nloc, dtype=torch.float64, device=dev),
+                      loss=torch.zeros(1, dtype=torch.float64, device=dev),
+                      ct=torch.zeros(self.nloc, self.K, dtype=torch.complex128, device=dev),
+                      cts=torch.zeros(self.nloc, dtype=torch.complex128, device=dev),
+                      stat=torch.zeros(self.nloc, dtype=torch.int32, device=dev))
+        self._lib = _lib
+
+    def step_device(self):
+        import torch
+        import torch.distributed as dist
+        d, st, vp = self.d, self.st, self._lib.C.c_void_p
+        stream = torch.cuda.current_stream().cuda_stream
+        st.check(st.lib.jpb_eval_loss_grad_dev(
+            st.h, self.prob.solver_num, self.nloc, vp(d["coef"].data_ptr()), vp(d["s"].data_ptr()),
+            vp(d["ref"].data_ptr()), vp(d["w"].data_ptr()), 3, self.F_total, vp(d["fr"].data_ptr()),
+            vp(d["loss"].data_ptr()), vp(d["ct"].data_ptr()), vp(d["cts"].data_ptr()), vp(d["stat"].data_ptr()),
+            vp(stream)))
+        g = (torch.einsum("fk,fkp->p", d["ct"], d["dc"]) + torch.einsum("f,fp->p", d["cts"], d["ds"])).real
+        acc = torch.cat([d["loss"] / self.F_total, g])
+        if self.world > 1:
+            dist.all_reduce(acc)
+        return acc
+
+    def barrier(self):
+        import torch
+        import torch.distributed as dist
+        if self.world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed_device(self, steps):
+        import torch
+        import torch.distributed as dist
+        self.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+        e0.record()
+        out = None
+        for k in range(steps):
+            out = self.step_device()
+            marks[k].record()      # per-step boundaries (diagnostic only; the metric uses e0 -> e1)
+        e1.record()
+        self.barrier()
+        step_ms = [round(a.elapsed_time(b), 2) for a, b in zip([e0] + marks[:-1], marks)]
+        ms = torch.tensor([e0.elapsed_time(e1)], device=self.dev, dtype=torch.float64)
+        if self.world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item(), out, step_ms
+
+    def timed_e2e(self, steps, warmup):
+        """Public API with host buffers: H2D of the step's inputs and D2H of its results inside
+        the timed region (jpb_eval_loss_grad stages both through page-locked memory)."""
+        import gc
+        import torch
+        import torch.distributed as dist
+        for _ in range(warmup):
+            self.loss.value_and_grad(PARAMS)
+        self.barrier()
+        gc.collect()
+        gc.disable()          # as timeit does: no collector pause inside the timed region
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            L, g = self.loss.value_and_grad(PARAMS)
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], device=self.dev, dtype=torch.float64)
+        gc.enable()
+        if self.world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        return dt.item(), L, g
+
+    def e2e_bytes(self):
+        n, K = self.nloc, self.K      # the two pinned-staging transfers of eval_host (engine.cu)
+        return int((n * (K * 16 + 16 + 8 + 4) + 32 + 15) // 16 * 16), int(n * (K * 16 + 16 + 8 + 4) + 8 + 16)
+
+    def close(self):
+        import torch
+        self.d = None
+        self.st.close()
+        torch.cuda.empty_cache()
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
     from plate_inverse_problem_b200 import _lib
-    from plate_inverse_problem_b200.Material import SOL
-    from plate_inverse_problem_b200.Problem import AP1030, Geometry, Problem
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -238,159 +424,137 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    hbm_peak = json.load(open(peaks_file))["hbm_gbs"] if os.path.exists(peaks_file) else 6650.0
+    hbm_src = "MEASURED_PEAKS.json" if os.path.exists(peaks_file) else "fallback of B200_PROFILING.md"
+    # FP64 tensor-core peak BEFORE anything heats the part (MEASURED_PEAKS.json has no FP64 figure)
+    st0 = _lib.State(local)
+    peak = np.zeros(1)
+    st0.check(st0.lib.jpb_dmma_peak(st0.h, _lib.ptr(peak)))
+    st0.close()
+    dmma_peak = float(peak[0])
+
     wl = args.workload
+    strong = args.scaling == "strong"
     F_local = args.freqs or FREQS_PER_GPU.get(wl, 128)
-    F_total = F_local * world
-    plate = make_inputs(wl)
-    prob = Problem(Geometry(H, plate), SOL(RHO, ANGLES, *PARAMS), AP1030, device=local)
-    info = prob.symbolic_info()
-    freqs = np.linspace(40.0, 600.0, F_total)
-    # synthetic reference FRF: forward run at perturbed parameters (cpu_benchmark.py:30 style)
-    pert = PARAMS * np.array([1.1, 1.1, 1.2, 1.0, 1.5])
-    ref_fr = prob.solveForward(freqs, pert)
-    loss = prob.getLossFunction(freqs, ref_fr, "MSE_LOG_AFC")
-
-    # ---- device-resident arm: inputs already in HBM, one C-ABI call per step --------------
-    lo, hi = (F_total * rank) // world, (F_total * (rank + 1)) // world
-    coef, s, dc, ds = prob.coefficients(freqs[lo:hi], PARAMS, with_jacobian=True)
-    nloc, K, P = hi - lo, coef.shape[1], PARAMS.size
-    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
-    d_coef, d_s, d_ref, d_w = t(coef), t(s), t(ref_fr[lo:hi]), t(prob.weights)
-    d_dc, d_ds = t(dc), t(ds)
-    d_fr = torch.zeros(nloc, dtype=torch.float64, device=dev)
-    d_loss = torch.zeros(1, dtype=torch.float64, device=dev)
-    d_ct = torch.zeros(nloc, K, dtype=torch.complex128, device=dev)
-    d_cts = torch.zeros(nloc, dtype=torch.complex128, device=dev)
-    d_stat = torch.zeros(nloc, dtype=torch.int32, device=dev)
-    st = prob._st
-    vp = _lib.C.c_void_p
-
-    def step_device():
-        stream = torch.cuda.current_stream().cuda_stream
-        st.check(st.lib.jpb_eval_loss_grad_dev(
-            st.h, prob.solver_num, nloc, vp(d_coef.data_ptr()), vp(d_s.data_ptr()), vp(d_ref.data_ptr()),
-            vp(d_w.data_ptr()), 3, F_total, vp(d_fr.data_ptr()), vp(d_loss.data_ptr()), vp(d_ct.data_ptr()),
-            vp(d_cts.data_ptr()), vp(d_stat.data_ptr()), vp(stream)))
-        g = (torch.einsum("fk,fkp->p", d_ct, d_dc) + torch.einsum("f,fp->p", d_cts, d_ds)).real
-        acc = torch.cat([d_loss / F_total, g])
-        if world > 1:
-            dist.all_reduce(acc)
-        return acc
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, steps):
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        marks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
-        e0.record()
-        out = None
-        for k in range(steps):
-            out = fn()
-            marks[k].record()      # per-step boundaries (diagnostic only; the metric uses e0 -> e1)
-        e1.record()
-        barrier()
-        timed.step_ms = [round(a.elapsed_time(b), 2) for a, b in zip([e0] + marks[:-1], marks)]
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return ms.item(), out
-
+    F_total = F_local if strong else F_local * world
+    arm = Arm(wl, F_total, world, rank, local, dev)
+    st, info, nloc = arm.st, arm.info, arm.nloc
     if args.profile:        # short run for ncu: one warm-up step, one step, nothing else
-        step_device()
-        ms_dev, acc = timed(step_device, 1)
+        arm.step_device()
+        ms_dev, acc, _ = arm.timed_device(1)
         if rank == 0:
             print(json.dumps(dict(profile_run=True, ms=ms_dev, timings=st.timings())))
         return
-    for _ in range(max(args.warmup, 3)):
-        step_device()
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
+        arm.step_device()
     with ClockSampler(local) as clocks:
-        ms_dev, acc = timed(step_device, args.steps)
-        step_ms = timed.step_ms
+        ms_dev, acc, step_ms = arm.timed_device(args.steps)
         tm = st.timings()      # phase timers of the last step (CUDA events on the same stream)
-        # ---- end-to-end arm: public API, host buffers, H2D + D2H inside the timed region ---
-        # the host side of the public call (torch autograd of the material transform, ctypes,
-        # pinned staging) needs a few more calls than the kernels to reach steady state on a
-        # fresh box (observed 137 -> 107 -> 97 -> 80 ms over the first calls after 3 warm-ups)
-        for _ in range(max(args.warmup, E2E_WARMUP)):
-            loss.value_and_grad(PARAMS)
-        barrier()
-        import gc
-        gc.collect()
-        gc.disable()          # as timeit does: no collector pause inside the timed region
-        t0 = time.perf_counter()
-        trace, devms = [], []
-        for _ in range(args.steps):
-            L_e2e, g_e2e = loss.value_and_grad(PARAMS)
-            trace.append(time.perf_counter())
-            if os.environ.get("JPB_E2E_TRACE"):
-                devms.append(round(sum(v for k, v in st.timings().items() if k.endswith("_ms")), 1))
-        torch.cuda.synchronize()
-        dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
-        gc.enable()
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        e2e_s = dt.item()
-        if os.environ.get("JPB_E2E_TRACE"):
-            print("e2e per-step ms:", np.round(np.diff([t0] + trace) * 1e3, 1), "device ms:", devms, file=sys.stderr)
+        e2e_s, L_e2e, g_e2e = arm.timed_e2e(args.steps, max(args.warmup, E2E_WARMUP))
     acc = acc.cpu().numpy()
     assert np.allclose(acc[0], L_e2e, rtol=1e-9) and np.allclose(acc[1:], g_e2e, rtol=1e-7, atol=1e-12 * np.abs(g_e2e).max())
-    assert int(d_stat.max().item()) == 0
+    assert int(arm.d["stat"].max().item()) == 0
 
     value = F_total * args.steps / (ms_dev * 1e-3)
     e2e_value = F_total * args.steps / e2e_s
-    flops_step = info["flops"] * nloc
-    peak = np.zeros(1)
-    st.check(st.lib.jpb_dmma_peak(st.h, _lib.ptr(peak)))
-    fac_tf = flops_step / (tm["factor_ms"] * 1e-3) / 1e12
-    peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    hbm_peak = json.load(open(peaks_file))["hbm_gbs"] if os.path.exists(peaks_file) else 6650.0
-    solve_bytes = 16.0 * info["nnz_lu"] * nloc * (1 + st_refine(prob))     # one pass over L and U per solve
+    refine = st_refine(arm.prob)
+    fac_tf = info["flops"] * nloc / (tm["factor_ms"] * 1e-3) / 1e12
+    solve_bytes = 16.0 * min(info["nnz_lu"], CPU_FILL.get(wl, info["nnz_lu"])) * nloc * (1 + refine)
+    h2d, d2h = arm.e2e_bytes()
     line = None
     if rank == 0:
-        cb = None
+        cb = par = None
         if world == 1 and not args.no_cpu:
             cb, _, _ = cpu_baseline(wl, target_seconds=args.cpu_seconds)
+            par = parity_sample(arm.prob, arm.plate, wl, arm.freqs, arm.ref_fr, args.parity_freqs)
+        traffic, traffic_src = committed_factor_traffic(wl, nloc)
         line = dict(
-            metric=METRIC, value=value, unit="evals/s", n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
-            ms_per_step=ms_dev / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
-            dtype="c128", data="synthetic",
+            metric=METRIC, value=value, unit="evals/s", n_gpus=world, steps=args.steps, warmup=warm,
+            ms_per_step=ms_dev / args.steps, higher_is_better=True, scaling="strong" if strong else "weak",
+            vs_baseline=None, dtype="c128", data="synthetic",
             config=dict(workload=workload_name(wl), N=int(info["N"]), nnz=int(info["nnz"]),
-                        freqs_per_gpu=F_local, freqs_per_step=F_total, params=PARAMS.size,
-                        loss="MSE_LOG_AFC", refinement_steps=st_refine(prob), parallelism=f"freq-shard x{world}",
+                        freqs_per_gpu=nloc, freqs_per_step=F_total, params=PARAMS.size,
+                        loss="MSE_LOG_AFC", refinement_steps=refine, parallelism=f"freq-shard x{world}",
+                        systems_per_wave=int(tm["wave"]),
                         l2_policy="working set (fronts of one wave, %.1f GB) far exceeds the 126 MB L2; no flush needed"
                                   % (info["front_slots"] * 16 * min(nloc, tm["wave"]) / 1e9)),
-            e2e=dict(value=e2e_value, unit="evals/s",
-                     # the two pinned-staging transfers of jpb_eval_loss_grad (engine.cu)
-                     h2d_bytes_per_step=int((nloc * (K * 16 + 16 + 8) + 32 + 15) // 16 * 16),
-                     d2h_bytes_per_step=int(nloc * (K * 16 + 16 + 8 + 4) + 16),
+            e2e=dict(value=e2e_value, unit="evals/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h,
                      warmup=max(args.warmup, E2E_WARMUP)),
             gpu_launches=int(tm["launches"] * args.steps),
             step_ms=step_ms,
             clocks=clocks.summary(),
-            roofline=dict(bound="tensor", achieved=fac_tf, peak=float(peak[0]), unit="TFLOP/s",
-                          frac=fac_tf / float(peak[0]),
-                          traffic=FACTOR_DRAM_BYTES.get((wl, nloc)),
-                          traffic_note="dram__bytes_read+write summed over the factor launches of one "
-                                       "wave (ncu launch list profiles/r1o_launches_cfg1_F400.csv)",
-                          kernel="numeric factorisation of one wave: factor_smem_kernel (fronts <= 64) + "
+            roofline=dict(bound="tensor", achieved=fac_tf, peak=dmma_peak, unit="TFLOP/s", frac=fac_tf / dmma_peak,
+                          traffic=traffic,
+                          traffic_note=(f"dram__bytes_read+write summed over the factor launches of one step, ncu "
+                                        f"launch list {traffic_src}") if traffic else
+                                       "no committed ncu launch list for this workload / batch size",
+                          kernel="numeric factorisation of one step: factor_smem_kernel (fronts <= 64) + "
                                  "factor_level_kernel (larger fronts), all levels",
-                          note="FP64 DMMA (mma.sync m8n8k4) peak measured live by jpb_dmma_peak; "
-                               "MEASURED_PEAKS.json holds no FP64 figure",
-                          flops_per_system=info["flops"], systems_per_launch_group=nloc),
+                          note="FP64 DMMA (mma.sync m8n8k4) peak measured live by jpb_dmma_peak BEFORE the timed "
+                               "loops; MEASURED_PEAKS.json holds no FP64 figure",
+                          flops_per_system=info["flops"], systems_per_launch_group=int(min(nloc, tm["wave"])),
+                          whole_step=whole_step_roofline(info, arm.K, nloc, refine, hbm_peak, dmma_peak,
+                                                         ms_dev / args.steps, wl),
+                          hbm_peak_source=hbm_src),
             phases_ms=dict(factor=tm["factor_ms"], fwd_solve=tm["fwd_solve_ms"], adj_solve=tm["adj_solve_ms"],
                            spmv=tm["spmv_ms"], grad=tm["grad_ms"], readout=tm["readout_ms"]),
             solve_hbm=dict(achieved_gbs=solve_bytes / (tm["fwd_solve_ms"] * 1e-3) / 1e9, peak_gbs=hbm_peak,
                            frac=solve_bytes / (tm["fwd_solve_ms"] * 1e-3) / 1e9 / hbm_peak,
-                           bytes_per_system=16.0 * info["nnz_lu"]),
-            cpu_baseline=cb,
+                           bytes_per_system=solve_bytes / nloc / (1 + refine)),
+            cpu_baseline=cb, parity=par,
         )
+    arm.close()
+    del arm
+
+    # ---- north-star configuration: fixed sweep of the ~1e5-DOF plate split over the GPUs ----
+    if not args.no_north_star and wl == "cfg1" and not strong:
+        ns = north_star(args, world, rank, local, dev, dmma_peak, hbm_peak)
+        if rank == 0:
+            line["north_star"] = ns
+    if rank == 0:
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def north_star(args, world, rank, local, dev, dmma_peak, hbm_peak):
+    wl, F_total = NORTH_STAR[0], args.north_star_freqs or NORTH_STAR[1]
+    arm = Arm(wl, F_total, world, rank, local, dev)
+    steps = max(1, min(args.steps, 2))
+    arm.step_device()
+    ms_dev, acc, step_ms = arm.timed_device(steps)
+    tm = arm.st.timings()
+    e2e_s, L_e2e, g_e2e = arm.timed_e2e(1, 1)
+    acc = acc.cpu().numpy()
+    assert np.allclose(acc[0], L_e2e, rtol=1e-9) and np.allclose(acc[1:], g_e2e, rtol=1e-7, atol=1e-12 * np.abs(g_e2e).max())
+    assert int(arm.d["stat"].max().item()) == 0
+    info, nloc = arm.info, arm.nloc
+    out = None
+    if rank == 0:
+        cb = par = None
+        if world == 1 and not args.no_cpu:
+            cb, _, _ = cpu_baseline(wl, target_seconds=args.cpu_seconds)
+            par = parity_sample(arm.prob, arm.plate, wl, arm.freqs, arm.ref_fr, 3)
+        fac_tf = info["flops"] * nloc / (tm["factor_ms"] * 1e-3) / 1e12      # timers sum over the waves
+        out = dict(metric=METRIC, value=F_total * steps / (ms_dev * 1e-3), unit="evals/s", n_gpus=world,
+                   scaling="strong", steps=steps, warmup=1, ms_per_step=ms_dev / steps, step_ms=step_ms,
+                   config=dict(workload=workload_name(wl), N=int(info["N"]), nnz=int(info["nnz"]),
+                               freqs_per_step=F_total, freqs_per_gpu=nloc, systems_per_wave=int(tm["wave"]),
+                               waves_per_gpu=int(-(-nloc // max(1, int(tm["wave"])))), loss="MSE_LOG_AFC",
+                               parallelism=f"freq-shard x{world}, one all-reduce of [loss, grad]"),
+                   e2e=dict(value=F_total / e2e_s, unit="evals/s", h2d_bytes_per_step=arm.e2e_bytes()[0],
+                            d2h_bytes_per_step=arm.e2e_bytes()[1], steps=1, warmup=1),
+                   roofline=dict(bound="tensor", unit="TFLOP/s", peak=dmma_peak, achieved=fac_tf,
+                                 frac=fac_tf / dmma_peak, note="factor phase, all waves of the last step",
+                                 whole_step=whole_step_roofline(info, arm.K, nloc, st_refine(arm.prob), hbm_peak,
+                                                                dmma_peak, ms_dev / steps, wl)),
+                   phases_ms=dict(factor=tm["factor_ms"], fwd_solve=tm["fwd_solve_ms"],
+                                            adj_solve=tm["adj_solve_ms"], spmv=tm["spmv_ms"], grad=tm["grad_ms"]),
+                   cpu_baseline=cb, parity=par)
+    arm.close()
+    return out
 
 
 def st_refine(prob):
@@ -404,9 +568,14 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg1")
-    ap.add_argument("--freqs", type=int, default=0, help="frequencies per GPU per step")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --freqs per GPU; strong: --freqs in total, split over the GPUs")
+    ap.add_argument("--freqs", type=int, default=0, help="frequencies per GPU (weak) / in total (strong) per step")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
-    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--parity-freqs", type=int, default=6)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU arm and the oracle parity sample")
+    ap.add_argument("--no-north-star", action="store_true")
+    ap.add_argument("--north-star-freqs", type=int, default=0)
     ap.add_argument("--profile", action="store_true", help="short device-only run (for ncu)")
     args = ap.parse_args()
     if args.impl == "reference":

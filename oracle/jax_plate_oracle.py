@@ -113,6 +113,33 @@ def umfpack_standin_lu(A):
                      options=dict(SymmetricMode=True))
 
 
+class OrderedLU:
+    """SuperLU with a caller-supplied symmetric fill-reducing ordering: factor P A P^T with
+    `permc_spec="NATURAL"`, same diagonal-pivot threshold as `umfpack_standin_lu`.  Used where
+    SuperLU's own MMD ordering does not finish (N ~ 1e5: SURVEY 8d asks for a CPU arm there);
+    `perm[new] = old`, e.g. the nested-dissection ordering of the symbolic phase."""
+
+    def __init__(self, A, perm, diag_pivot_thresh=1e-5):
+        # Threshold: with 1e-3 (UMFPACK's sym_pivot_tolerance, used by umfpack_standin_lu)
+        # SuperLU leaves the diagonal on the 210x80 plate and the fill triples (7.1e7 instead
+        # of 2.0e7 entries, 26 s instead of 2.5-3 s per factorisation on one core here, residual
+        # 4e-10 instead of 2e-11); with <= 1e-5 every pivot stays on the diagonal.  The faster,
+        # more accurate setting is the one timed as CPU baseline (conservative for the GPU).
+        self.perm = np.asarray(perm)
+        Ap = sps.csc_matrix(A)[self.perm][:, self.perm].tocsc()
+        self.lu = spla.splu(Ap, permc_spec="NATURAL", diag_pivot_thresh=diag_pivot_thresh,
+                            options=dict(SymmetricMode=True))
+
+    def solve(self, b, trans="N"):
+        x = np.empty_like(b)
+        x[self.perm] = self.lu.solve(np.ascontiguousarray(b[self.perm]), trans=trans)
+        return x
+
+    @property
+    def nnz_lu(self):
+        return int(self.lu.L.nnz + self.lu.U.nnz - self.perm.size)
+
+
 def solve_extended(A, b, trans=False, iters=6):
     """High-accuracy solve used to judge BOTH the stand-in LU and the CUDA path: SuperLU as
     preconditioner, residual accumulated in 80-bit extended precision (np.clongdouble), so
@@ -428,7 +455,8 @@ class OracleProblem:
     (SURVEY §3.2, §3.3, App. D): per frequency one numeric LU for the forward solve and a
     second one for the transposed (adjoint) solve (`InnerState.h:276-288` called twice)."""
 
-    def __init__(self, plate, transform, inertia, acc_h, acc_h_eff, acc_ts):
+    def __init__(self, plate, transform, inertia, acc_h, acc_h_eff, acc_ts, ordering=None):
+        self.ordering = ordering      # None: SuperLU's MMD; else perm[new] = old for OrderedLU
         self.plate = plate
         self.N = plate.N
         self.nz_idx, (self.row, self.col), self.native, self.mats = \
@@ -442,6 +470,9 @@ class OracleProblem:
         self.solver_num = self.state.add_mat(n["N"], n["indices"], n["indptr"], n["indices_T"],
                                              n["indptr_T"], n["permutation"])
 
+    def factor(self, A):
+        return umfpack_standin_lu(A) if self.ordering is None else OrderedLU(A, self.ordering)
+
     def matrix(self, coef_row):
         n = self.native
         return sps.csc_matrix((assemble(coef_row, self.mats), n["indices"], n["indptr"]),
@@ -454,13 +485,27 @@ class OracleProblem:
         fr = np.zeros(coef.shape[0])
         self._lus = []
         for i in range(coef.shape[0]):
-            lu = umfpack_standin_lu(self.matrix(coef[i]))
+            lu = self.factor(self.matrix(coef[i]))
             U[i] = lu.solve(s[i] * self.plate.rhs_vec.astype(np.complex128))
             y = self.Q @ U[i]
             fr[i] = np.sqrt(ts ** 2 * abs(y[0]) ** 2 + ts ** 2 * abs(y[1]) ** 2 + abs(y[2]) ** 2)
             if reuse_factor:
                 self._lus.append(lu)
         return (fr, U) if return_u else fr
+
+    def fr_jacobian(self, freqs, params):
+        """J[f, p] = d fr_f / d p_p, the matrix `jax.jacobian` of `getFRFunction` would give
+        (the Gauss-Newton model of `Optimizers.py:139-144` is built from it): the adjoint
+        formula of `loss_and_grad` with the cotangent of fr itself (dL/dfr = 1 per row)."""
+        freqs = np.atleast_1d(np.asarray(freqs, dtype=np.float64))
+        J = np.zeros((freqs.size, len(params)))
+        fr = np.zeros(freqs.size)
+        for i, f in enumerate(freqs):
+            # MSE against ref = 0 with F = 1: L = fr^2, dL/dp = 2 fr dfr/dp
+            L, g, aux = self.loss_and_grad(np.array([f]), params, np.zeros(1), "MSE", reuse_factor=True)
+            fr[i] = aux["fr"][0]
+            J[i] = g / (2.0 * fr[i])
+        return fr, J
 
     def loss_and_grad(self, freqs, params, ref, func_type, reuse_factor=False):
         """JAX convention (App. D): u_bar = dL/dRe(u) - i dL/dIm(u), lambda = A^-T u_bar,
@@ -485,7 +530,7 @@ class OracleProblem:
             if reuse_factor:
                 lam = self._lus[i].solve(ubar, trans="T")
             else:
-                lu = umfpack_standin_lu(self.matrix(coef[i]))
+                lu = self.factor(self.matrix(coef[i]))
                 lam = lu.solve(ubar, trans="T")
             ctA = -lam[self.row] * U[i][self.col]      # Sparse.py:173-176 (with the JVP sign)
             ct_coef[i] = self.mats @ ctA

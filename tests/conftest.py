@@ -20,7 +20,7 @@ ANGLES = (0, 45, -45, 90)
 class Case:
     """A synthetic plate + the oracle problem on it (SURVEY 8d inputs)."""
 
-    def __init__(self, nx, ny):
+    def __init__(self, nx, ny, nd_ordering=False):
         from oracle import jax_plate_oracle as orc
         from plate_inverse_problem_b200.Problem import AP1030
         from plate_inverse_problem_b200.synthetic import make_plate
@@ -32,6 +32,11 @@ class Case:
                                     AP1030.effective_height, AP1030.transverse_sensitivity)
         self.N = self.plate.N
         self.native = self.op.native
+        if nd_ordering:
+            # SuperLU's own MMD ordering does not finish at N ~ 1e5; the oracle then factors
+            # P A P^T with the nested-dissection ordering of the (host-only) symbolic phase
+            from plate_inverse_problem_b200 import _lib
+            self.op.ordering = _lib.host_symbolic(self.N, self.native["indices"], self.native["indptr"])["perm"]
 
     def problem(self, **kw):
         from plate_inverse_problem_b200.Material import SOL
@@ -50,7 +55,7 @@ _cases = {}
 def get_case(name):
     from plate_inverse_problem_b200.synthetic import NAMED_SIZES
     if name not in _cases:
-        _cases[name] = Case(*NAMED_SIZES[name])
+        _cases[name] = Case(*NAMED_SIZES[name], nd_ordering=name in ("40k", "cfg4", "cfg5"))
     return _cases[name]
 
 
