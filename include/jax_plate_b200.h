@@ -58,6 +58,13 @@ const char* jpb_last_error(const jpb_state* st);
 int jpb_set_memory_budget(jpb_state* st, int64_t bytes);
 /* iterative-refinement steps applied after every triangular solve (default 1) */
 int jpb_set_refinement(jpb_state* st, int steps);
+/* adaptive refinement on top of the unconditional steps: up to `extra_steps` further steps
+ * (default 2), each executed only for the systems whose last correction was still larger than
+ * tol * ||x|| (max-norms, default 1e-11) -- in a frequency sweep these are the few systems next
+ * to a resonance, where cond(A) times the backward error of the static-pivot factorisation is
+ * not << 1; the other systems' blocks exit at once.  umfpack_zi_solve refines the same way
+ * (until the backward error stops improving, at most 2 steps by default). */
+int jpb_set_adaptive_refinement(jpb_state* st, int extra_steps, double tol);
 /* number of concurrent sub-waves (CUDA streams) a fused evaluation is cut into (default 1;
  * 1 = strictly sequential phases, which is what the per-phase timers of jpb_last_timings
  * need to be meaningful).  No counterpart in the reference (OpenMP over items,
@@ -65,12 +72,13 @@ int jpb_set_refinement(jpb_state* st, int steps);
 int jpb_set_streams(jpb_state* st, int n);
 /* Residual acceptance.  Pivoting is static with partial pivoting inside the 32-wide pivot
  * tiles only, which is safe for the plate matrices of jax_plate but
- * not for arbitrary ones, so every system is also judged by its residual:
- *   jpb_solve      : ||b - A x|| <= tol_final * ||b|| for the solution returned (one more
- *                    pass over A per call; default 1e-8);
- *   jpb_eval_*     : the residual of the UNREFINED solution must be <= tol_unrefined * ||b||
- *                    (default 1e-5; the refinement step that follows squares it), tested on
- *                    the residual the refinement computes anyway -- no extra pass.
+ * not for arbitrary ones, so every system is also judged by its normwise backward error
+ * omega = ||b - A x||_2 / || |A| |x| + |b| ||_2 (moduli in the 1-norm of (re, im)):
+ *   jpb_solve      : omega <= tol_final for the solution returned (one more pass over A per
+ *                    call; default 1e-10; a healthy solve gives ~1e-16);
+ *   jpb_eval_*     : omega of the UNREFINED solution <= tol_unrefined (default 1e-6; the
+ *                    refinement step that follows contracts it by ~cond(A) * omega), tested
+ *                    on the residual the refinement computes anyway -- no extra pass.
  * A system that fails gets status bit 2 and the call returns JPB_ESINGULAR.  (UMFPACK's
  * threshold pivoting has no such restriction; the reference raises only for status != 0,
  * umfpack_interface.h:11-18.) */
@@ -103,7 +111,7 @@ int jpb_get_ordering(const jpb_state* st, int solver_num, int32_t* perm);
  * nbatch0 = B (modes 1-3) or B0 (mode 4); nbatch1 = B1 (mode 4 only).
  * transpose != 0 solves A^T x = b (plain transpose, UMFPACK_Aat, InnerState.h:183-185).
  * status (optional, one int per system): bit 0 (1) zero / non-finite pivot block, bit 1 (2)
- * relative residual above the tolerance of jpb_set_residual_tolerance. */
+ * backward error above the tolerance of jpb_set_residual_tolerance. */
 int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const double* data,
               const double* b, int64_t nbatch0, int64_t nbatch1, double* out, int* status);
 int jpb_matvec(jpb_state* st, int solver_num, int mode, int transpose, const double* mat,

@@ -140,6 +140,28 @@ class OrderedLU:
         return int(self.lu.L.nnz + self.lu.U.nnz - self.perm.size)
 
 
+class ExtendedLU:
+    """A factorisation whose `solve` refines in 80-bit extended precision (`solve_extended`
+    with a factorisation the caller already has): the answer is the exact solution of the
+    assembled system to ~1e-16, which is what BOTH the stand-in LU and the CUDA path are
+    judged against where cond(A) * eps exceeds the parity tolerances (next to resonances)."""
+
+    def __init__(self, A, lu, iters=6):
+        self.lu, self.iters = lu, iters
+        Ac = sps.coo_matrix(A)
+        self.r, self.c, self.v = Ac.row, Ac.col, Ac.data.astype(np.clongdouble)
+
+    def solve(self, b, trans="N"):
+        r_, c_ = (self.c, self.r) if trans == "T" else (self.r, self.c)
+        bl = np.asarray(b).astype(np.clongdouble)
+        x = self.lu.solve(np.asarray(b, dtype=np.complex128), trans=trans).astype(np.clongdouble)
+        for _ in range(self.iters):
+            Ax = np.zeros(bl.size, dtype=np.clongdouble)
+            np.add.at(Ax, r_, self.v * x[c_])
+            x = x + self.lu.solve((bl - Ax).astype(np.complex128), trans=trans).astype(np.clongdouble)
+        return x.astype(np.complex128)
+
+
 def solve_extended(A, b, trans=False, iters=6):
     """High-accuracy solve used to judge BOTH the stand-in LU and the CUDA path: SuperLU as
     preconditioner, residual accumulated in 80-bit extended precision (np.clongdouble), so
@@ -457,6 +479,7 @@ class OracleProblem:
 
     def __init__(self, plate, transform, inertia, acc_h, acc_h_eff, acc_ts, ordering=None):
         self.ordering = ordering      # None: SuperLU's MMD; else perm[new] = old for OrderedLU
+        self.exact = False            # True: every solve refined in extended precision (ExtendedLU)
         self.plate = plate
         self.N = plate.N
         self.nz_idx, (self.row, self.col), self.native, self.mats = \
@@ -471,7 +494,8 @@ class OracleProblem:
                                              n["indptr_T"], n["permutation"])
 
     def factor(self, A):
-        return umfpack_standin_lu(A) if self.ordering is None else OrderedLU(A, self.ordering)
+        lu = umfpack_standin_lu(A) if self.ordering is None else OrderedLU(A, self.ordering)
+        return ExtendedLU(A, lu) if self.exact else lu
 
     def matrix(self, coef_row):
         n = self.native

@@ -160,12 +160,15 @@ struct jpb_state {
     std::string err;
     int64_t budget = 0;
     int refine = 1;
-    // residual acceptance (status bit 2): jpb_solve checks the FINAL residual against
-    // resid_tol; the fused path checks the residual BEFORE the refinement correction against
-    // resid_tol0 (one step squares it) at no extra pass over A
-    double resid_tol = 1e-8, resid_tol0 = 1e-5;
+    int refine_extra = 2;          // adaptive steps on top, only for vectors not yet converged
+    double refine_tol = 1e-11;     // ... i.e. last correction > refine_tol * ||x|| (max-norms)
+    // residual acceptance (status bit 2) on the normwise backward error
+    // omega = ||b - A x|| / || |A||x| + |b| ||: jpb_solve checks omega of what it returns against
+    // resid_tol; the fused path checks omega of the UNREFINED solution against resid_tol0 (the
+    // refinement step that follows contracts it by ~cond(A) * omega) at no extra pass over A
+    double resid_tol = 1e-10, resid_tol0 = 1e-6;
     // workspaces
-    DevBuf F, V, vals, data, vb, vx, vr, vd, vlam, partial, small, hstage, status, norms, lterm;
+    DevBuf F, V, vals, data, vb, vx, vr, vd, vlam, partial, small, hstage, status, norms, lterm, active;
     PinBuf pin;
     // instrumentation
     std::vector<TimedSpan> spans;
@@ -242,7 +245,7 @@ int fail(jpb_state* st, int code, const char* fmt, ...) {
 const char* status_message(int bits) {
     if (bits & 1) return "matrix is singular (zero pivot block)";
     return "matrix is singular to working precision or badly scaled for static pivoting: the "
-           "relative residual of a system exceeds the tolerance (jpb_set_residual_tolerance)";
+           "backward error (residual) of a system exceeds the tolerance (jpb_set_residual_tolerance)";
 }
 
 #define JPB_TRY(st) try {
@@ -434,7 +437,7 @@ void tri_solve(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool tran
 // y(b,j) = [rhs(b,j) -] op(A_b) x(b,j)
 void spmv(jpb_state* st, cudaStream_t s, Pattern& P, bool trans, const cd* vals, int64_t vals_sb,
           bool vals_ent_order, const cd* x, int64_t x_sb, int64_t x_sj, const cd* rhs, int64_t rhs_sb,
-          int64_t rhs_sj, cd* y, int nsys, int nrhs, double* norms = nullptr) {
+          int64_t rhs_sj, cd* y, int nsys, int nrhs, double* norms = nullptr, const int* active = nullptr) {
     Span span(st, s, PH_SPMV);
     const int* ptr = trans ? P.d_csc_ptr : P.d_csr_ptr;
     const int* idx = trans ? P.d_csc_row : P.d_csr_col;
@@ -442,8 +445,12 @@ void spmv(jpb_state* st, cudaStream_t s, Pattern& P, bool trans, const cd* vals,
                            : (vals_ent_order ? P.d_csr_pos_ent : P.d_csr_pos);
     dim3 grid((P.S.N + 127) / 128, (unsigned)(nsys * nrhs));
     if ((int64_t)nsys * nrhs > 65535) throw InvalidArg("too many vectors for one spmv launch");
-    spmv_kernel<<<grid, 128, 0, s>>>(P.S.N, P.S.nnz, ptr, idx, pos, vals, vals_sb, x, x_sb, x_sj, rhs,
-                                     rhs_sb, rhs_sj, y, nsys, norms);
+    if (norms)
+        spmv_kernel<true><<<grid, 128, 0, s>>>(P.S.N, P.S.nnz, ptr, idx, pos, vals, vals_sb, x, x_sb, x_sj, rhs,
+                                               rhs_sb, rhs_sj, y, nsys, norms, active);
+    else
+        spmv_kernel<false><<<grid, 128, 0, s>>>(P.S.N, P.S.nnz, ptr, idx, pos, vals, vals_sb, x, x_sb, x_sj, rhs,
+                                                rhs_sb, rhs_sj, y, nsys, norms, active);
     launch_check(st);
 }
 
@@ -452,26 +459,36 @@ void solve_refined(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool 
                    int64_t vals_sb, bool vals_ent_order, const cd* rhs, int64_t rhs_sb, int64_t rhs_sj,
                    cd* x, cd* V, cd* r, cd* d, int nsys, int nrhs, int phase, int* status,
                    bool final_check) {
-    VecView vv{rhs, rhs_sb, rhs_sj, x, V, nsys, nrhs};
+    VecView vv{rhs, rhs_sb, rhs_sj, x, V, nsys, nrhs, nullptr};
     tri_solve(st, s, P, F, trans, vv, phase);
     const int nvec = nsys * nrhs;
+    // steps 0 .. refine-1 are unconditional; up to refine_extra more run only for the vectors
+    // whose last correction was still above refine_tol * ||x|| (the systems next to a resonance,
+    // where cond(A) * (backward error of the static-pivot factorisation) is not << 1)
+    const int nsteps = st->refine + (st->refine > 0 ? st->refine_extra : 0);
+    int* active = nsteps > st->refine ? (int*)st->active.get((size_t)nvec * sizeof(int)) : nullptr;
     double* norms = nullptr;
     if (status && (final_check || st->refine > 0)) norms = (double*)st->norms.get((size_t)nvec * 16);
     auto flag = [&](double tol) {
         residual_flag_kernel<<<(nvec + 127) / 128, 128, 0, s>>>(nvec, nsys, norms, tol * tol, status);
         launch_check(st);
     };
-    for (int it = 0; it < st->refine; ++it) {
+    for (int it = 0; it < nsteps; ++it) {
+        const int* act = it >= st->refine ? active : nullptr;
         // the residual of the unrefined solution doubles as the acceptance test of the fused path
         double* nrm = (norms && !final_check && it == 0) ? norms : nullptr;
         if (nrm) CK(cudaMemsetAsync(nrm, 0, (size_t)nvec * 16, s));
-        spmv(st, s, P, trans, vals, vals_sb, vals_ent_order, x, 1, nsys, rhs, rhs_sb, rhs_sj, r, nsys, nrhs, nrm);
+        spmv(st, s, P, trans, vals, vals_sb, vals_ent_order, x, 1, nsys, rhs, rhs_sb, rhs_sj, r, nsys, nrhs, nrm, act);
         if (nrm) flag(st->resid_tol0);
-        VecView v2{r, 1, nsys, d, V, nsys, nrhs};
+        VecView v2{r, 1, nsys, d, V, nsys, nrhs, act};
         tri_solve(st, s, P, F, trans, v2, phase);
-        int64_t n = (int64_t)nsys * nrhs * P.S.N;
-        axpy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, x, d);
+        dim3 grid((P.S.N + 255) / 256, nvec);
+        axpy_kernel<<<grid, 256, 0, s>>>(P.S.N, x, d, act);
         launch_check(st);
+        if (active && it + 1 >= st->refine && it + 1 < nsteps) {
+            refine_active_kernel<<<nvec, 256, 0, s>>>(P.S.N, x, d, st->refine_tol, active, it + 1 == st->refine);
+            launch_check(st);
+        }
     }
     if (norms && final_check) {      // ||b - A x|| / ||b|| of what is returned (jpb_solve)
         CK(cudaMemsetAsync(norms, 0, (size_t)nvec * 16, s));
@@ -705,6 +722,14 @@ int jpb_set_streams(jpb_state* st, int n) {
 int jpb_set_refinement(jpb_state* st, int steps) {
     if (!st || steps < 0 || steps > 8) return fail(st, JPB_EINVAL, "refinement steps must be in [0, 8]");
     st->refine = steps;
+    return JPB_OK;
+}
+
+int jpb_set_adaptive_refinement(jpb_state* st, int extra_steps, double tol) {
+    if (!st || extra_steps < 0 || extra_steps > 8 || !(tol >= 0.0))
+        return fail(st, JPB_EINVAL, "adaptive refinement: steps in [0, 8], tol >= 0");
+    st->refine_extra = extra_steps;
+    st->refine_tol = tol;
     return JPB_OK;
 }
 

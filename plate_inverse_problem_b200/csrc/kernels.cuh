@@ -979,6 +979,10 @@ struct VecView {
     cd* x;              // x(b, j)   = x + (j * nsys + b) * N
     cd* V;              // front-local vectors, (j * nsys + b) * vec_slots
     int nsys, nrhs;
+    // adaptive refinement: when non-null, vectors with active[j * nsys + b] == 0 are skipped
+    // (their blocks / warps exit at once), so a late refinement step costs only the systems
+    // that still need it
+    const int* active;
 };
 
 // Forward sweep over one level.  TRANS = false: Lt (unit block lower);  TRANS = true:
@@ -995,6 +999,7 @@ fwd_level_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __re
     const int b = bid % vv.nsys;
     bid /= vv.nsys;
     const int jr = bid % vv.nrhs;
+    if (vv.active && !vv.active[jr * vv.nsys + b]) return;
     const FrontDesc fd = sd.fr[level_fronts[bid / vv.nrhs]];
     const cd* F = Fall + (int64_t)b * sd.front_slots + fd.off;
     cd* V = vv.V + ((int64_t)jr * vv.nsys + b) * sd.vec_slots;
@@ -1079,6 +1084,7 @@ bwd_level_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __re
     const int b = bid % vv.nsys;
     bid /= vv.nsys;
     const int jr = bid % vv.nrhs;
+    if (vv.active && !vv.active[jr * vv.nsys + b]) return;
     const FrontDesc fd = sd.fr[level_fronts[bid / vv.nrhs]];
     const cd* F = Fall + (int64_t)b * sd.front_slots + fd.off;
     const cd* Vf = vv.V + ((int64_t)jr * vv.nsys + b) * sd.vec_slots + fd.voff;
@@ -1201,7 +1207,7 @@ fwd_warp_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __res
     const int nvec = vv.nsys * vv.nrhs;
     const int groups = (nvec + NW - 1) / NW;
     const int vec = (blockIdx.x % groups) * NW + warp;
-    if (vec >= nvec) return;          // no block-wide barrier below
+    if (vec >= nvec || (vv.active && !vv.active[vec])) return;          // no block-wide barrier below
     const int b = vec % vv.nsys, jr = vec / vv.nsys;
     const FrontDesc fd = sd.fr[level_fronts[blockIdx.x / groups]];
     const cd* F = Fall + (int64_t)b * sd.front_slots + fd.off;
@@ -1273,7 +1279,7 @@ bwd_warp_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __res
     const int nvec = vv.nsys * vv.nrhs;
     const int groups = (nvec + NW - 1) / NW;
     const int vec = (blockIdx.x % groups) * NW + warp;
-    if (vec >= nvec) return;
+    if (vec >= nvec || (vv.active && !vv.active[vec])) return;
     const int b = vec % vv.nsys;
     const FrontDesc fd = sd.fr[level_fronts[blockIdx.x / groups]];
     const cd* F = Fall + (int64_t)b * sd.front_slots + fd.off;
@@ -1338,15 +1344,20 @@ bwd_warp_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __res
 // y(b, j) = [rhs(b, j) -] sum_{q in ptr[i]..ptr[i+1]} vals[b, pos[q]] * x(b, j)[idx[q]]
 // (ptr, idx, pos) is the CSR view for A x and the CSC view for A^T x; pos == nullptr
 // means identity.  grid.y = system * nrhs, one thread per row.
+template <bool NORMS>
 __global__ void spmv_kernel(int N, int64_t nnz, const int* __restrict__ ptr,
                             const int* __restrict__ idx, const int* __restrict__ pos,
                             const cd* __restrict__ vals, int64_t vals_sb,
                             const cd* __restrict__ x, int64_t x_sb, int64_t x_sj,
                             const cd* __restrict__ rhs, int64_t rhs_sb, int64_t rhs_sj,
-                            cd* y, int nsys, double* norms) {
+                            cd* y, int nsys, double* norms, const int* active) {
+    if (active && !active[blockIdx.y]) return;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int b = blockIdx.y % nsys, j = blockIdx.y / nsys;
-    double nr = 0.0, nb2 = 0.0;     // |r_i|^2 and |rhs_i|^2 of this row (residual check)
+    // residual check: |r_i|^2 and t_i^2 with t_i = sum_e |a_e| |x_e| + |rhs_i| (1-norm moduli),
+    // i.e. the ingredients of the normwise backward error ||r|| / || |A||x| + |b| ||
+    double nr = 0.0, nb2 = 0.0, tacc = 0.0;
+    auto m1 = [](cd v) { return fabs(v.x) + fabs(v.y); };
     if (i < N) {
     const cd* vb = vals + (int64_t)b * vals_sb * nnz;
     const cd* xb = x + ((int64_t)j * x_sj + (int64_t)b * x_sb) * N;
@@ -1364,6 +1375,10 @@ __global__ void spmv_kernel(int N, int64_t nnz, const int* __restrict__ ptr,
         for (int u = 0; u < 8; ++u) { a[u] = vb[pq[u]]; xv[u] = xb[jq[u]]; }
 #pragma unroll
         for (int u = 0; u < 8; ++u) cfma(acc, a[u], xv[u]);
+        if (NORMS) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) tacc = fma(m1(a[u]), m1(xv[u]), tacc);
+        }
     }
     for (; q + 4 <= q1; q += 4) {
         int pq[4], jq[4];
@@ -1374,24 +1389,33 @@ __global__ void spmv_kernel(int N, int64_t nnz, const int* __restrict__ ptr,
         for (int u = 0; u < 4; ++u) { a[u] = vb[pq[u]]; xv[u] = xb[jq[u]]; }
 #pragma unroll
         for (int u = 0; u < 4; ++u) cfma(acc, a[u], xv[u]);
+        if (NORMS) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) tacc = fma(m1(a[u]), m1(xv[u]), tacc);
+        }
     }
     for (; q < q1; ++q) {
         cd a = vb[pos ? pos[q] : q];
-        cfma(acc, a, xb[idx[q]]);
+        const cd xv = xb[idx[q]];
+        cfma(acc, a, xv);
+        if (NORMS) tacc = fma(m1(a), m1(xv), tacc);
     }
     cd* yb = y + ((int64_t)j * nsys + b) * N;
     if (rhs) {
         cd r = rhs[((int64_t)j * rhs_sj + (int64_t)b * rhs_sb) * N + i];
         acc.x = r.x - acc.x;
         acc.y = r.y - acc.y;
-        nr = acc.x * acc.x + acc.y * acc.y;
-        nb2 = r.x * r.x + r.y * r.y;
+        if (NORMS) {
+            nr = acc.x * acc.x + acc.y * acc.y;
+            tacc += m1(r);
+            nb2 = tacc * tacc;
+        }
     }
     yb[i] = acc;
     }
-    // norms[(j * nsys + b) * 2 + {0, 1}] += sum_i {|r_i|^2, |rhs_i|^2}: feeds the per-system
+    // norms[(j * nsys + b) * 2 + {0, 1}] += sum_i {|r_i|^2, t_i^2}: feeds the per-system
     // residual check (status bit 2); the summation order is irrelevant for a threshold test
-    if (norms) {
+    if (NORMS) {
         __shared__ double red[2][32];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -1417,7 +1441,7 @@ __global__ void spmv_kernel(int N, int64_t nnz, const int* __restrict__ ptr,
     }
 }
 
-// status[vec % nsys] |= 2 where ||r||^2 > tol2 * ||rhs||^2 (or the residual is not finite)
+// status[vec % nsys] |= 2 where ||r||^2 > tol2 * || |A||x| + |b| ||^2 (or the residual is not finite)
 __global__ void residual_flag_kernel(int nvec, int nsys, const double* __restrict__ norms, double tol2,
                                      int* status) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1426,10 +1450,43 @@ __global__ void residual_flag_kernel(int nvec, int nsys, const double* __restric
     if (!(nr <= tol2 * nb) && !(nr == 0.0)) atomicOr(status + v % nsys, 2);
 }
 
-// x += d
-__global__ void axpy_kernel(int64_t n, cd* x, const cd* __restrict__ d) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) { cd a = x[i], c = d[i]; a.x += c.x; a.y += c.y; x[i] = a; }
+// x += d  (vector v = blockIdx.y; skipped when inactive)
+__global__ void axpy_kernel(int N, cd* x, const cd* __restrict__ d, const int* __restrict__ active) {
+    const int v = blockIdx.y;
+    if (active && !active[v]) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) {
+        const int64_t q = (int64_t)v * N + i;
+        cd a = x[q], c = d[q];
+        a.x += c.x; a.y += c.y;
+        x[q] = a;
+    }
+}
+
+// Convergence test of the refinement: one CTA per vector; the vector stays active while the
+// correction just applied is larger than tol * ||x|| (max-norms), otherwise it is retired.
+__global__ void refine_active_kernel(int N, const cd* __restrict__ x, const cd* __restrict__ d, double tol,
+                                     int* active, int first) {
+    __shared__ double red[2][32];
+    const int v = blockIdx.x;
+    if (!first && !active[v]) return;
+    double md = 0.0, mx = 0.0;
+    for (int i = threadIdx.x; i < N; i += blockDim.x) {
+        const cd a = d[(int64_t)v * N + i], b = x[(int64_t)v * N + i];
+        md = fmax(md, fmax(fabs(a.x), fabs(a.y)));
+        mx = fmax(mx, fmax(fabs(b.x), fabs(b.y)));
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        md = fmax(md, __shfl_xor_sync(0xffffffffu, md, o));
+        mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = md; red[1][threadIdx.x >> 5] = mx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { md = fmax(md, red[0][w]); mx = fmax(mx, red[1][w]); }
+        // NaN-safe: a non-finite correction retires the vector (the residual test reports it)
+        active[v] = (md > tol * mx) && (md == md) && (md < 1e300) ? 1 : 0;
+    }
 }
 
 // data[b, e] = sum_k coef[b,k] * mats[k,e]   (K1; HBM-bound: reads K*8 B, writes 16 B per entry)

@@ -209,6 +209,22 @@ def rules_fixture(pkg, prob, rec):
     return out
 
 
+def input_fixture(pkg):
+    """`Input.Compressor` (`Input.py:5-158`) of the reference on a synthetic FRF with several
+    resonances (the oracle's forward sweep of the tiny plate, 1500 points)."""
+    from conftest import get_case
+    case = get_case("tiny")
+    freqs = np.linspace(40.0, 1200.0, 1500)
+    fr = case.op.forward(freqs, PARAMS).astype(np.complex128) * np.exp(0.3j)
+    out = dict(in_freqs=freqs, in_fr=fr)
+    for alg in (0, 1):
+        for want in (30, 200, 317, 1000):
+            c = pkg.Input.Compressor(freqs, fr, 1200, alg)
+            f_sel, _ = c(want)
+            out[f"mask_alg{alg}_{want}"] = np.isin(freqs, f_sel)
+    return out
+
+
 def check(pkg):
     """--check: recompute the quick parts and compare with the committed fixtures."""
     bad = []
@@ -217,13 +233,14 @@ def check(pkg):
         for k, v in new.items():
             o = old[k]
             v = np.asarray(v)
-            if v.dtype.kind in "iuUS" or k.endswith("_sha"):
+            if v.dtype.kind in "biuUS" or k.endswith("_sha"):
                 ok = np.array_equal(v, o)
             else:
                 ok = v.shape == o.shape and np.max(np.abs(v - o)) <= tol * max(np.max(np.abs(o)), 1e-300)
             if not ok:
                 bad.append(f"{tag}:{k}")
     cmp("transforms", transform_fixture(pkg), np.load(os.path.join(OUT, "ref_transforms.npz")), 1e-14)
+    cmp("input", input_fixture(pkg), np.load(os.path.join(OUT, "ref_input.npz")), 1e-11)
     tiny, prob, rec = problem_fixture(pkg, "tiny", 9, full=False)
     tiny.update(rules_fixture(pkg, prob, rec))
     cmp("tiny", tiny, np.load(os.path.join(OUT, "ref_tiny.npz")), 1e-11)
@@ -237,6 +254,9 @@ def main():
     pkg = ref_shim.load("compiled")
     if "--check" in sys.argv:
         return check(pkg)
+    np.savez_compressed(os.path.join(OUT, "ref_input.npz"), **input_fixture(pkg))
+    if "--only-input" in sys.argv:
+        return
     np.savez_compressed(os.path.join(OUT, "ref_transforms.npz"), **transform_fixture(pkg))
     tiny, prob, rec = problem_fixture(pkg, "tiny", 9, full=True)
     tiny.update(rules_fixture(pkg, prob, rec))

@@ -159,7 +159,7 @@ def _install_stubs(inner_state_cls):
     jnp.__getattr__ = lambda name: getattr(np, name)
     jax = types.ModuleType("jax")
     jax.numpy = jnp
-    jax.Array = np.ndarray
+    jax.Array = type("Array", (), {})       # annotations only; must NOT be np.ndarray (scipy's array-api probes)
     jax.jit = _jit
     jax.vmap = _vmap
     jax.value_and_grad = _value_and_grad
@@ -172,6 +172,7 @@ def _install_stubs(inner_state_cls):
     core = types.ModuleType("jax.core")
     core.Primitive = Primitive
     core.ShapedArray = ShapedArray
+    core.Tracer = type("Tracer", (), {})
     jax.core = core
     interp = types.ModuleType("jax.interpreters")
     ad = types.ModuleType("jax.interpreters.ad")
