@@ -59,11 +59,12 @@ int jpb_set_memory_budget(jpb_state* st, int64_t bytes);
 /* iterative-refinement steps applied after every triangular solve (default 1) */
 int jpb_set_refinement(jpb_state* st, int steps);
 /* adaptive refinement on top of the unconditional steps: up to `extra_steps` further steps
- * (default 2), each executed only for the systems whose last correction was still larger than
- * tol * ||x|| (max-norms, default 1e-11) -- in a frequency sweep these are the few systems next
- * to a resonance, where cond(A) times the backward error of the static-pivot factorisation is
- * not << 1; the other systems' blocks exit at once.  umfpack_zi_solve refines the same way
- * (until the backward error stops improving, at most 2 steps by default). */
+ * (default 0 = off), each executed only for the systems whose last correction was still larger
+ * than tol * ||x|| (max-norms, default 1e-11); the other systems' blocks exit at once.  Meant
+ * for matrices on which the static-pivot factorisation has a poor backward error, so that one
+ * step does not reach the working-precision floor.  For the plate sweeps one step does
+ * (measured: further steps move u by less than cond(A) * eps), hence off.
+ * umfpack_zi_solve refines until the backward error stops improving, at most 2 steps. */
 int jpb_set_adaptive_refinement(jpb_state* st, int extra_steps, double tol);
 /* number of concurrent sub-waves (CUDA streams) a fused evaluation is cut into (default 1;
  * 1 = strictly sequential phases, which is what the per-phase timers of jpb_last_timings

@@ -230,6 +230,8 @@ class Problem:
 
         loss.value_and_grad = value_and_grad
         loss.grad = lambda params: value_and_grad(params)[1]
+        # the Gauss-Newton model of the same loss, for Optimizers.optimize_lm / method="gn"
+        loss.gauss_newton = self.getGaussNewtonModel(frequencies, reference_fr, func_type, scaling_params)
         loss.__name__ = func_type + "Loss"
         return loss
 

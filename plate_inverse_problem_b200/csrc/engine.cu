@@ -160,7 +160,8 @@ struct jpb_state {
     std::string err;
     int64_t budget = 0;
     int refine = 1;
-    int refine_extra = 2;          // adaptive steps on top, only for vectors not yet converged
+    int refine_extra = 0;          // adaptive steps on top, only for vectors not yet converged (off by default:
+                                   // measured, they do not move the plate systems)
     double refine_tol = 1e-11;     // ... i.e. last correction > refine_tol * ||x|| (max-norms)
     // residual acceptance (status bit 2) on the normwise backward error
     // omega = ||b - A x|| / || |A||x| + |b| ||: jpb_solve checks omega of what it returns against

@@ -225,6 +225,79 @@ def input_fixture(pkg):
     return out
 
 
+class Rosenbrock:
+    """Analytic objective carrying its own derivatives, so that the reference's optimiser
+    loops (`Optimizers.py`) run under the shim: f, value_and_grad, grad_fn(.jacobian = Hessian)."""
+
+    def __init__(self, a=10.0):
+        self.a = a
+        outer = self
+
+        class _Grad:
+            def __call__(self, x):
+                return outer.value_and_grad(x)[1]
+
+            def jacobian(self, x):
+                return outer.hessian(x)
+        self.grad_fn = _Grad()
+
+    def __call__(self, x):
+        x = np.asarray(x, dtype=np.float64)
+        return float(np.sum(self.a * (x[1:] - x[:-1] ** 2) ** 2 + (1 - x[:-1]) ** 2))
+
+    def value_and_grad(self, x):
+        x = np.asarray(x, dtype=np.float64)
+        g = np.zeros_like(x)
+        d = x[1:] - x[:-1] ** 2
+        g[:-1] += -4 * self.a * d * x[:-1] - 2 * (1 - x[:-1])
+        g[1:] += 2 * self.a * d
+        return self(x), g
+
+    def hessian(self, x):
+        x = np.asarray(x, dtype=np.float64)
+        n = x.size
+        H = np.zeros((n, n))
+        for i in range(n - 1):
+            H[i, i] += -4 * self.a * (x[i + 1] - 3 * x[i] ** 2) + 2
+            H[i, i + 1] += -4 * self.a * x[i]
+            H[i + 1, i] += -4 * self.a * x[i]
+            H[i + 1, i + 1] += 2 * self.a
+        return H
+
+
+def optimizer_fixture(pkg):
+    """The reference's optimiser loops (`Optimizers.py:153-286`) and trust-region sub-problem
+    solver (`:70-122`) on an analytic objective.  (`optimize_cd_mem2` differentiates a local
+    closure with jax and cannot run under the shim.)"""
+    O = pkg.Optimizers
+    f = Rosenbrock()
+    x0 = np.array([-0.8, 0.6, 0.3])
+    out = dict(opt_x0=x0)
+    runs = dict(gd=lambda: O.optimize_gd(f, x0.copy(), N_steps=40, h=0.01, f_min=1e-8),
+                cd=lambda: O.optimize_cd(f, x0.copy(), N_steps=15, h=0.01, f_min=1e-8),
+                tr=lambda: O.optimize_trust_region(f, x0.copy(), N_steps=25, delta_max=1.0))
+    for name, run in runs.items():
+        r = run()
+        out[f"opt_{name}_x"] = np.asarray(r.x, dtype=np.float64)
+        out[f"opt_{name}_f"] = np.array(float(r.f))
+        out[f"opt_{name}_fhist"] = np.array([float(v) for v in r.f_history])
+        out[f"opt_{name}_ghist"] = np.array([np.asarray(g, dtype=np.float64) for g in r.grad_history])
+        out[f"opt_{name}_niter"] = np.array(int(r.niter))
+        out[f"opt_{name}_status"] = np.array(str(r.status))
+    rng = np.random.default_rng(5)
+    for i in range(6):
+        M = rng.standard_normal((4, 4))
+        B = M + M.T + (3.0 if i % 2 == 0 else -0.5) * np.eye(4)      # definite and indefinite models
+        g = rng.standard_normal(4)
+        delta = [0.05, 0.5, 5.0][i % 3]
+        sd, lam, pred = O.solve_trust_region_model(B, g, delta)
+        out[f"trm_{i}_B"], out[f"trm_{i}_g"], out[f"trm_{i}_delta"] = B, g, np.array(delta)
+        out[f"trm_{i}_sd"], out[f"trm_{i}_lam"], out[f"trm_{i}_pred"] = np.asarray(sd), np.array(float(lam)), np.array(float(pred))
+    fp = O.FixedParameterFunction(f, 3, 1, 0.6)
+    out["fixed_val"] = np.array(float(fp(np.array([-0.8, 0.3]))))
+    return out
+
+
 def check(pkg):
     """--check: recompute the quick parts and compare with the committed fixtures."""
     bad = []
@@ -241,6 +314,7 @@ def check(pkg):
                 bad.append(f"{tag}:{k}")
     cmp("transforms", transform_fixture(pkg), np.load(os.path.join(OUT, "ref_transforms.npz")), 1e-14)
     cmp("input", input_fixture(pkg), np.load(os.path.join(OUT, "ref_input.npz")), 1e-11)
+    cmp("optim", optimizer_fixture(pkg), np.load(os.path.join(OUT, "ref_optim.npz")), 1e-11)
     tiny, prob, rec = problem_fixture(pkg, "tiny", 9, full=False)
     tiny.update(rules_fixture(pkg, prob, rec))
     cmp("tiny", tiny, np.load(os.path.join(OUT, "ref_tiny.npz")), 1e-11)
@@ -255,6 +329,7 @@ def main():
     if "--check" in sys.argv:
         return check(pkg)
     np.savez_compressed(os.path.join(OUT, "ref_input.npz"), **input_fixture(pkg))
+    np.savez_compressed(os.path.join(OUT, "ref_optim.npz"), **optimizer_fixture(pkg))
     if "--only-input" in sys.argv:
         return
     np.savez_compressed(os.path.join(OUT, "ref_transforms.npz"), **transform_fixture(pkg))

@@ -123,6 +123,31 @@ class Primitive:
         return out
 
 
+class _At:
+    def __init__(self, arr, idx=None):
+        self.arr, self.idx = arr, idx
+
+    def __getitem__(self, idx):
+        return _At(self.arr, idx)
+
+    def set(self, value):
+        out = np.array(self.arr)
+        out[self.idx] = value
+        return out.view(_JArr)
+
+
+class _JArr(np.ndarray):
+    """ndarray with jax's functional update `x.at[idx].set(v)` (`Optimizers.py:54-55`)."""
+
+    @property
+    def at(self):
+        return _At(self)
+
+
+def _jnp_array(*a, **k):
+    return np.array(*a, **k).view(_JArr)
+
+
 def _vmap(fn, in_axes=0, out_axes=0):
     def mapped(*args):
         axes = in_axes if isinstance(in_axes, (tuple, list)) else (in_axes,) * len(args)
@@ -146,6 +171,8 @@ def _value_and_grad(f, *a, **k):
 
 
 def _grad(f, *a, **k):
+    if hasattr(f, "grad_fn"):          # an object that may in turn carry .jacobian (Hessian)
+        return f.grad_fn
     vg = _value_and_grad(f)
     return lambda x: vg(x)[1]
 
@@ -154,9 +181,16 @@ def _no_ad(*a, **k):
     raise NotImplementedError("ref_shim: no automatic differentiation")
 
 
+def _jacobian(g, *a, **k):
+    if hasattr(g, "jacobian"):
+        return g.jacobian
+    return _no_ad()
+
+
 def _install_stubs(inner_state_cls):
     jnp = types.ModuleType("jax.numpy")
     jnp.__getattr__ = lambda name: getattr(np, name)
+    jnp.array = _jnp_array
     jax = types.ModuleType("jax")
     jax.numpy = jnp
     jax.Array = type("Array", (), {})       # annotations only; must NOT be np.ndarray (scipy's array-api probes)
@@ -164,7 +198,8 @@ def _install_stubs(inner_state_cls):
     jax.vmap = _vmap
     jax.value_and_grad = _value_and_grad
     jax.grad = _grad
-    jax.jacobian = jax.hessian = jax.jacfwd = jax.jacrev = _no_ad
+    jax.jacobian = _jacobian
+    jax.hessian = jax.jacfwd = jax.jacrev = _no_ad
     jax.config = types.SimpleNamespace(update=lambda *a, **k: None)
     tree_util = types.ModuleType("jax.tree_util")
     tree_util.Partial = functools.partial
