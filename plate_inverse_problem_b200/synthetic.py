@@ -89,6 +89,56 @@ def rectangle_mesh(nx: int, ny: int, Lx: float, Ly: float) -> PlateMesh:
     return PlateMesh(points, tris, edges, tri_edges, clamped_v, clamped_e, Lx, Ly)
 
 
+def mesh_from_triangulation(points, tris, clamped_vertex_mask) -> PlateMesh:
+    """A `PlateMesh` from ANY conforming triangulation (what FreeFem++'s `buildmesh` hands the
+    reference for an arbitrary `.edp` geometry, `pyFFInterface.py:279-336`): orients the
+    triangles counter-clockwise, numbers the edges, drops unused vertices, and flags as clamped
+    the edges whose two vertices are clamped AND that lie on the boundary."""
+    points = np.asarray(points, dtype=np.float64)
+    tris = np.asarray(tris, dtype=np.int64)
+    used = np.zeros(points.shape[0], dtype=bool)
+    used[tris.ravel()] = True
+    remap = np.cumsum(used) - 1
+    points, tris = points[used], remap[tris]
+    clamped_v = np.asarray(clamped_vertex_mask, dtype=bool)[used]
+    p = points[tris]
+    det = ((p[:, 1, 0] - p[:, 0, 0]) * (p[:, 2, 1] - p[:, 0, 1])
+           - (p[:, 2, 0] - p[:, 0, 0]) * (p[:, 1, 1] - p[:, 0, 1]))
+    if np.any(det == 0):
+        raise ValueError("degenerate triangle in the mesh")
+    flip = det < 0
+    tris[flip] = tris[flip][:, [0, 2, 1]]
+    loc = np.stack([tris[:, [1, 2]], tris[:, [2, 0]], tris[:, [0, 1]]], axis=1)
+    loc_sorted = np.sort(loc, axis=2)
+    nv = points.shape[0]
+    key = loc_sorted[..., 0] * nv + loc_sorted[..., 1]
+    ukey, inv, cnt = np.unique(key.ravel(), return_inverse=True, return_counts=True)
+    if np.any(cnt > 2):
+        raise ValueError("non-manifold mesh: an edge belongs to more than two triangles")
+    edges = np.stack([ukey // nv, ukey % nv], axis=1)
+    boundary = cnt == 1
+    clamped_e = clamped_v[edges[:, 0]] & clamped_v[edges[:, 1]] & boundary
+    ext = points.max(axis=0) - points.min(axis=0)
+    return PlateMesh(points, tris, edges, inv.reshape(-1, 3), clamped_v, clamped_e, float(ext[0]), float(ext[1]))
+
+
+def shaped_plate_mesh(nx: int, ny: int, Lx: float, Ly: float, keep) -> PlateMesh:
+    """Structured triangulation of the rectangle with the cells whose centre fails
+    `keep(xc, yc)` removed (L-shapes, notches, holes with a staircase boundary): a "complex
+    geometry" without a mesh generator.  The edge x = Lx stays the clamped one."""
+    base = rectangle_mesh(nx, ny, Lx, Ly)
+    cent = base.points[base.tris].mean(axis=1)
+    # both triangles of a cell share the cell centre up to the diagonal split: decide per cell
+    I, J = np.meshgrid(np.arange(nx), np.arange(ny), indexing="ij")
+    xc = (I.ravel() + 0.5) * Lx / nx
+    yc = -Ly / 2 + (J.ravel() + 0.5) * Ly / ny
+    keep_cell = np.asarray(keep(xc, yc), dtype=bool)
+    keep_tri = np.concatenate([keep_cell, keep_cell])
+    del cent
+    tol = 1e-12 * max(Lx, Ly)
+    return mesh_from_triangulation(base.points, base.tris[keep_tri], np.abs(base.points[:, 0] - Lx) < tol)
+
+
 def _p1_gradients(mesh: PlateMesh):
     p = mesh.points[mesh.tris]                     # [nt,3,2]
     x, y = p[..., 0], p[..., 1]
@@ -179,33 +229,44 @@ class SyntheticPlate:
                 self.Mh_size, self.mesh, self.interp_mat_Wx, self.interp_mat_Wy)
 
 
-def _locate(mesh: PlateMesh, pts: np.ndarray, nx: int, ny: int):
-    """Triangle id and barycentric coordinates of points in the structured mesh."""
-    Lx, Ly = mesh.Lx, mesh.Ly
-    fx = np.clip(pts[:, 0] / Lx * nx, 0, nx - 1e-9)
-    fy = np.clip((pts[:, 1] + Ly / 2) / Ly * ny, 0, ny - 1e-9)
-    i, j = fx.astype(int), fy.astype(int)
-    lx, ly = fx - i, fy - j
-    cell = i * ny + j
-    lower = ly <= lx                      # triangle (v00, v10, v11)
-    tri = np.where(lower, cell, cell + nx * ny)
-    p = mesh.points[mesh.tris[tri]]
-    T = np.stack([p[:, 1] - p[:, 0], p[:, 2] - p[:, 0]], axis=2)   # [n,2,2]
-    rhs = pts - p[:, 0]
-    lam12 = np.linalg.solve(T, rhs[..., None])[..., 0]
-    lam = np.concatenate([1 - lam12.sum(1, keepdims=True), lam12], axis=1)
+def _locate(mesh: PlateMesh, pts: np.ndarray):
+    """Triangle id and barycentric coordinates of points in ANY triangulation: the triangle
+    whose smallest barycentric coordinate is largest (inside: >= 0; a point in a hole or
+    outside snaps to the nearest triangle in that sense)."""
+    p = mesh.points[mesh.tris]                                     # [nt,3,2]
+    T = np.stack([p[:, 1] - p[:, 0], p[:, 2] - p[:, 0]], axis=2)   # [nt,2,2]
+    Tinv = np.linalg.inv(T)
+    tri = np.zeros(pts.shape[0], dtype=np.int64)
+    lam = np.zeros((pts.shape[0], 3))
+    for k, x in enumerate(pts):
+        l12 = np.einsum("tij,tj->ti", Tinv, x[None, :] - p[:, 0])
+        lall = np.concatenate([1 - l12.sum(1, keepdims=True), l12], axis=1)
+        t = int(np.argmax(lall.min(axis=1)))
+        tri[k], lam[k] = t, lall[t]
     return tri, lam
 
 
 def make_plate(nx: int, ny: int, Lx: float = 99.9e-3, Ly: float = 20e-3,
-               r_accel: float = 3.8e-3, n_readout: int = 16) -> SyntheticPlate:
-    mesh = rectangle_mesh(nx, ny, Lx, Ly)
+               r_accel: float = 3.8e-3, n_readout: int = 16, keep=None) -> SyntheticPlate:
+    """Rectangular cantilever plate (`keep=None`) or a shaped one: `keep(xc, yc) -> bool` per
+    cell centre (see `shaped_plate_mesh`).  The accelerometer sits in the corner of the free
+    end, `sh_i.edp:11-15`."""
+    mesh = rectangle_mesh(nx, ny, Lx, Ly) if keep is None else shaped_plate_mesh(nx, ny, Lx, Ly, keep)
+    return plate_from_mesh(mesh, (r_accel, Ly / 2 - r_accel), r_accel, n_readout)
+
+
+def plate_from_mesh(mesh: PlateMesh, test_point, r_accel: float = 3.8e-3, n_readout: int = 16) -> SyntheticPlate:
+    """The 26 component matrices, right-hand side and read-out operators of
+    `load_matrices_unsymm` (`pyFFInterface.py:169-509`) on an ARBITRARY conforming
+    triangulation: P1 for (u, v), Morley for w, Dirichlet rows with tgv = -1 on the clamped
+    vertices / edges of `mesh`, accelerometer disc of radius `r_accel` around `test_point`."""
+    Ly = mesh.Ly
     nv, ne, nt = mesh.points.shape[0], mesh.edges.shape[0], mesh.tris.shape[0]
     Lh, Mh = nv, nv + ne
     N = 2 * Lh + Mh
 
     area, gx, gy = _p1_gradients(mesh)
-    xtest, ytest = r_accel, Ly / 2 - r_accel          # sh_i.edp:11-15
+    xtest, ytest = test_point
     cent = mesh.points[mesh.tris].mean(axis=1)
     ind = ((cent[:, 0] - xtest) ** 2 + (cent[:, 1] - ytest) ** 2 <= r_accel ** 2 + 1e-8)
     ind = ind.astype(np.float64)                      # indAccel, sh_i.edp:34
@@ -362,7 +423,7 @@ def make_plate(nx: int, ny: int, Lx: float = 99.9e-3, Ly: float = 20e-3,
     th = np.linspace(0.0, 2 * np.pi, n_readout, endpoint=False)
     rp = np.stack([xtest + 0.3 * r_accel * np.cos(th), ytest + 0.3 * r_accel * np.sin(th)], 1)
     rp = np.concatenate([rp, [[xtest, ytest]]], axis=0)
-    tri, lam = _locate(mesh, rp, nx, ny)
+    tri, lam = _locate(mesh, rp)
     npts = rp.shape[0]
     interp_L = np.zeros((npts, Lh))
     np.add.at(interp_L, (np.arange(npts)[:, None], mesh.tris[tri]), lam)
@@ -395,3 +456,61 @@ NAMED_SIZES = {
     "cfg4": (210, 80),       # N = 101 963 (configs[3])
     "cfg5": (160, 50),       # N ~ 4.9e4   (configs[4])
 }
+
+
+def _lshape_with_hole(Lx, Ly):
+    """L-shaped plate (the quadrant x < 0.45 Lx, y < -0.1 Ly removed) with a circular hole."""
+    def keep(xc, yc):
+        notch = (xc < 0.45 * Lx) & (yc < -0.1 * Ly)
+        hole = (xc - 0.7 * Lx) ** 2 + (yc + 0.1 * Ly) ** 2 < (0.18 * Ly) ** 2
+        return ~(notch | hole)
+    return keep
+
+
+# "complex-geometry" plates (BASELINE configs[3]): same outer box, cells removed
+SHAPED_SIZES = {
+    "tinyL": (12, 6),        # N ~ 5e2
+    "smallL": (40, 12),      # N ~ 2.6e3
+    "cfg4L": (240, 96),      # N ~ 1.0e5   (configs[3], complex geometry)
+}
+
+
+def make_named(name: str) -> SyntheticPlate:
+    """`make_plate` for a name of NAMED_SIZES (rectangles) or SHAPED_SIZES (L-shape + hole)."""
+    if name in SHAPED_SIZES:
+        nx, ny = SHAPED_SIZES[name]
+        return make_plate(nx, ny, keep=_lshape_with_hole(99.9e-3, 20e-3))
+    return make_plate(*NAMED_SIZES[name])
+
+
+def save_plate(path, plate: SyntheticPlate) -> None:
+    """On-disk format of the hot path's inputs (the tuple of `pyFFInterface.py:503-509` plus
+    the mesh): one .npz with the 26 component matrices as concatenated COO triplets
+    (`coo_row`, `coo_col`, `coo_data`, `coo_ptr[27]`; explicit zeros kept, they are part of the
+    pattern), `rhs_vec`, the dense read-out operators and the mesh arrays."""
+    rows = [m.row.astype(np.int64) for m in plate.mats]
+    ptr = np.concatenate([[0], np.cumsum([r.size for r in rows])])
+    np.savez_compressed(
+        path, format=np.array("jax_plate_b200.plate.v1"), names=np.array(COMPONENT_NAMES),
+        N=np.array(plate.N), Lh=np.array(plate.Lh_size), Mh=np.array(plate.Mh_size), coo_ptr=ptr,
+        coo_row=np.concatenate(rows), coo_col=np.concatenate([m.col.astype(np.int64) for m in plate.mats]),
+        coo_data=np.concatenate([m.data for m in plate.mats]), rhs_vec=plate.rhs_vec,
+        interp_mat=plate.interp_mat, interp_mat_Lh=plate.interp_mat_Lh, interp_mat_Wx=plate.interp_mat_Wx,
+        interp_mat_Wy=plate.interp_mat_Wy, test_point=np.array(plate.test_point),
+        mesh_points=plate.mesh.points, mesh_tris=plate.mesh.tris, mesh_edges=plate.mesh.edges,
+        mesh_tri_edges=plate.mesh.tri_edges, mesh_clamped_vertices=plate.mesh.clamped_vertices,
+        mesh_clamped_edges=plate.mesh.clamped_edges, mesh_extent=np.array([plate.mesh.Lx, plate.mesh.Ly]))
+
+
+def load_plate(path) -> SyntheticPlate:
+    z = np.load(path, allow_pickle=False)
+    if str(z["format"]) != "jax_plate_b200.plate.v1":
+        raise ValueError(f"{path}: not a plate file of this package")
+    N, ptr = int(z["N"]), z["coo_ptr"]
+    mats = [sps.coo_matrix((z["coo_data"][a:b], (z["coo_row"][a:b], z["coo_col"][a:b])), shape=(N, N))
+            for a, b in zip(ptr[:-1], ptr[1:])]
+    mesh = PlateMesh(z["mesh_points"], z["mesh_tris"], z["mesh_edges"], z["mesh_tri_edges"],
+                     z["mesh_clamped_vertices"], z["mesh_clamped_edges"], float(z["mesh_extent"][0]),
+                     float(z["mesh_extent"][1]))
+    return SyntheticPlate(mats, z["rhs_vec"], z["interp_mat"], z["interp_mat_Lh"], int(z["Lh"]), int(z["Mh"]),
+                          mesh, z["interp_mat_Wx"], z["interp_mat_Wy"], tuple(z["test_point"]))

@@ -373,16 +373,21 @@ def test_benchmark_size_parity(name, nfreq):
     the 4e4-DOF plate and configs[3]), on a regular sweep over 40-600 Hz PLUS the three
     frequencies next to the 100 Hz resonance (99.65, 100.35, 101.75 Hz).
 
-    At these sizes cond(A) * eps reaches 1e-8 ... 1e-5, i.e. ANY two LU solvers -- and any two
-    roundings of the assembled entries -- differ by more than the north-star tolerances; the
-    SuperLU stand-in itself is that far from the exact solution.  The yardstick is therefore
-    the exact answer (the stand-in refined in 80-bit extended precision, oracle.ExtendedLU):
-      (E) end to end: FRF, loss, gradient, u of the CUDA path are within the north-star
-          tolerance of the exact answer, or within 4x of the stand-in's own distance to it;
-      (S) solver alone: on the matrix exactly as the DEVICE assembled it, u is within 1e-10 of
-          that matrix's exact solution or within 4x of what SuperLU achieves on the same matrix;
-      (A) assembly alone: device-assembled entries equal the oracle's up to 26 roundings of
-          sum_k |c_k m_k|.
+    At these sizes cond(A) reaches 1e8 ... 1e11, so one ulp in the assembled entries -- let
+    alone the choice of LU -- moves u by 1e-8 ... 1e-5: the SuperLU stand-in itself is that
+    far from the exact solution, and two assemblies that round differently (numpy's grouped
+    sums here, XLA's fusion in the reference, one FMA chain on the device) disagree by as
+    much.  The test therefore separates the three sources, with the exact answer (the
+    stand-in refined in 80-bit extended precision, oracle.ExtendedLU) as yardstick:
+      (A) assembly: device-assembled entries equal the oracle's up to 26 roundings of
+          sum_k |c_k m_k| per entry;
+      (S) everything after the assembly -- factorisation, both solves, read-out, loss,
+          adjoint, gradient contraction -- on the matrices EXACTLY as the device assembled
+          them: u, FRF, loss and gradient are within the north-star tolerances (1e-10 / 1e-8)
+          of the exact answer, or within 4x of what the stand-in LU achieves on the same
+          matrices (it never needs more than 1x in practice: see the log);
+      (E) end to end against the oracle's own matrices: u within (S) plus the distance between
+          the exact solutions of the two assemblies (triangle inequality).
     Every number is appended to gpurun_out/parity_r2.jsonl."""
     from plate_inverse_problem_b200 import _lib
     case = get_case(name)
@@ -390,55 +395,68 @@ def test_benchmark_size_parity(name, nfreq):
     op = case.op
     freqs = np.sort(np.concatenate([np.linspace(40.0, 600.0, nfreq), [99.65, 100.35, 101.75]]))
     F = freqs.size
-    fr_s, U_s = op.forward(freqs, PARAMS, return_u=True, reuse_factor=True)
-    ref = fr_s * (1.0 + 0.1 * np.cos(np.arange(F)))
-    std = {lt: op.loss_and_grad(freqs, PARAMS, ref, lt, reuse_factor=True)[:2] for lt in ("MSE_LOG_AFC", "MSE")}
-    op.exact = True
-    try:
-        fr_x, U_x = op.forward(freqs, PARAMS, return_u=True, reuse_factor=True)
-        ex = {lt: op.loss_and_grad(freqs, PARAMS, ref, lt, reuse_factor=True)[:2] for lt in ("MSE_LOG_AFC", "MSE")}
-    finally:
-        op.exact = False
+    lts = ("MSE_LOG_AFC", "MSE")
+    rel = lambda a, b: float(abs(a - b) / abs(b))
+
+    def oracle_run(exact):
+        op.exact = exact
+        try:
+            fr_, U_ = op.forward(freqs, PARAMS, return_u=True, reuse_factor=True)
+            lg = {lt: op.loss_and_grad(freqs, PARAMS, ref, lt, reuse_factor=True)[:2] for lt in lts}
+        finally:
+            op.exact = False
+        return fr_, U_, lg
+
+    # ---- the CUDA path ---------------------------------------------------------------------
     fr, y, u = prob._forward_raw(freqs, PARAMS, return_u=True)
-    ours = {lt: prob.getLossFunction(freqs, ref, lt).value_and_grad(PARAMS) for lt in ("MSE_LOG_AFC", "MSE")}
-    rel = lambda a, b: abs(a - b) / abs(b)
-    E = dict(u=(max(relerr(u[i], U_x[i]) for i in range(F)), max(relerr(U_s[i], U_x[i]) for i in range(F))),
-             fr=(float(np.max(np.abs(fr - fr_x) / fr_x)), float(np.max(np.abs(fr_s - fr_x) / fr_x))))
-    for lt in ("MSE_LOG_AFC", "MSE"):
-        E[f"loss_{lt}"] = (rel(ours[lt][0], ex[lt][0]), rel(std[lt][0], ex[lt][0]))
-        E[f"grad_{lt}"] = (relerr(ours[lt][1], ex[lt][1]), relerr(std[lt][1], ex[lt][1]))
-    vs_standin = dict(u=max(relerr(u[i], U_s[i]) for i in range(F)), fr=float(np.max(np.abs(fr - fr_s) / fr_s)),
-                      **{f"loss_{lt}": rel(ours[lt][0], std[lt][0]) for lt in std},
-                      **{f"grad_{lt}": relerr(ours[lt][1], std[lt][1]) for lt in std})
-    # (A) + (S) on the worst-conditioned and the last frequency
-    pick = [int(np.argmin(np.abs(freqs - 100.35))), F - 1]
-    coef, s_all = orc.coefficients(freqs[pick], PARAMS, case.transform, case.inertia)
+    ref = fr * (1.0 + 0.1 * np.cos(np.arange(F)))
+    ours = {lt: prob.getLossFunction(freqs, ref, lt).value_and_grad(PARAMS) for lt in lts}
+    # ---- (A) the matrices as the device assembles them -------------------------------------
+    coef, s_all = orc.coefficients(freqs, PARAMS, case.transform, case.inertia)
     nnz = op.mats.shape[1]
-    dev = np.zeros((len(pick), nnz), dtype=np.complex128)
+    dev = np.zeros((F, nnz), dtype=np.complex128)
     st = prob._st
-    st.check(st.lib.jpb_assemble(st.h, nnz, 26, len(pick), _lib.ptr(prob.mats), _lib.ptr(np.ascontiguousarray(coef)),
+    st.check(st.lib.jpb_assemble(st.h, nnz, 26, F, _lib.ptr(prob.mats), _lib.ptr(np.ascontiguousarray(coef)),
                                  _lib.ptr(dev)))
+    A_err = 0.0
+    for i in range(F):
+        scale = np.abs(coef[i]) @ np.abs(op.mats)
+        A_err = max(A_err, float(np.max(np.abs(dev[i] - orc.assemble(coef[i], op.mats)) / np.maximum(scale, 1e-300))))
+    # ---- oracle on the oracle's matrices and on the device's matrices ----------------------
+    fr_s, U_s, lg_s = oracle_run(False)
+    fr_x, U_x, lg_x = oracle_run(True)
     n = case.native
-    S, A_err = {}, 0.0
-    for j, i in enumerate(pick):
-        scale = np.abs(coef[j]) @ np.abs(op.mats)
-        A_err = max(A_err, float(np.max(np.abs(dev[j] - orc.assemble(coef[j], op.mats)) / np.maximum(scale, 1e-300))))
-        A = sps.csc_matrix((dev[j], n["indices"], n["indptr"]), shape=(case.N,) * 2)
-        b = s_all[j] * case.plate.rhs_vec.astype(np.complex128)
-        lu = op.factor(A)
-        xe = orc.ExtendedLU(A, lu).solve(b)
-        S[float(freqs[i])] = (relerr(u[i], xe), relerr(lu.solve(b), xe))
+    lookup = {coef[i].tobytes(): i for i in range(F)}
+    op.matrix = lambda c: sps.csc_matrix((dev[lookup[np.asarray(c).tobytes()]], n["indices"], n["indptr"]),
+                                         shape=(case.N,) * 2)
+    try:
+        fr_sd, U_sd, lg_sd = oracle_run(False)
+        fr_xd, U_xd, lg_xd = oracle_run(True)
+    finally:
+        del op.matrix
+    umax = lambda X, Y: max(relerr(X[i], Y[i]) for i in range(F))
+    S = dict(u=(umax(u, U_xd), umax(U_sd, U_xd)),
+             fr=(float(np.max(np.abs(fr - fr_xd) / fr_xd)), float(np.max(np.abs(fr_sd - fr_xd) / fr_xd))))
+    for lt in lts:
+        S[f"loss_{lt}"] = (rel(ours[lt][0], lg_xd[lt][0]), rel(lg_sd[lt][0], lg_xd[lt][0]))
+        S[f"grad_{lt}"] = (relerr(ours[lt][1], lg_xd[lt][1]), relerr(lg_sd[lt][1], lg_xd[lt][1]))
+    E = dict(u_cuda_vs_exact=umax(u, U_x), u_standin_vs_exact=umax(U_s, U_x),
+             u_exact_device_matrix_vs_exact_oracle_matrix=umax(U_xd, U_x),
+             u_cuda_vs_standin=umax(u, U_s), fr_cuda_vs_standin=float(np.max(np.abs(fr - fr_s) / fr_s)),
+             **{f"loss_{lt}_cuda_vs_standin": rel(ours[lt][0], lg_s[lt][0]) for lt in lts},
+             **{f"grad_{lt}_cuda_vs_standin": relerr(ours[lt][1], lg_s[lt][1]) for lt in lts},
+             **{f"loss_{lt}_standin_vs_exact": rel(lg_s[lt][0], lg_x[lt][0]) for lt in lts},
+             **{f"grad_{lt}_standin_vs_exact": relerr(lg_s[lt][1], lg_x[lt][1]) for lt in lts})
     _log(test="benchmark_size_parity", workload=name, N=case.N, freqs=freqs.tolist(),
-         cuda_vs_exact_and_standin_vs_exact={k: list(map(float, v)) for k, v in E.items()},
-         cuda_vs_standin={k: float(v) for k, v in vs_standin.items()},
-         solver_alone_u_cuda_and_superlu_vs_exact_of_device_matrix={k: list(v) for k, v in S.items()},
-         assembly_max_scaled_entry_error=A_err)
+         assembly_max_scaled_entry_error=A_err,
+         same_matrices_cuda_vs_exact_and_standin_vs_exact={k: list(map(float, v)) for k, v in S.items()},
+         end_to_end={k: float(v) for k, v in E.items()})
     assert A_err <= 26 * 1.2e-16, (name, A_err)
-    for f, (e_c, e_s) in S.items():
-        assert e_c <= max(TOL_U, 4 * e_s), (name, "solver", f, e_c, e_s)
     tols = dict(u=TOL_U, fr=1e-8)
-    for k, (e_c, e_s) in E.items():
-        assert e_c <= max(tols.get(k, TOL_LG), 4 * e_s), (name, k, e_c, e_s)
+    for k, (e_c, e_s) in S.items():
+        assert e_c <= max(tols.get(k, TOL_LG), 4 * e_s), (name, "same matrices", k, e_c, e_s)
+    assert E["u_cuda_vs_exact"] <= max(TOL_U, 4 * S["u"][1]) + 1.1 * E["u_exact_device_matrix_vs_exact_oracle_matrix"], \
+        (name, "end to end", E)
 
 
 @pytest.mark.parametrize("name,gold", [("tiny", REF_TINY), ("small", REF_SMALL)])

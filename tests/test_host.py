@@ -208,3 +208,60 @@ def test_optimizer_loops_follow_the_reference():
     assert np.allclose(r.x, xs, atol=1e-8)
     r = O.optimize_trust_region(q, np.zeros(2), N_steps=30, delta_max=10.0, method="newt")   # FD Hessian
     assert np.allclose(r.x, xs, atol=1e-6)
+
+
+def test_general_triangulation_assembler_and_npz_format(tmp_path):
+    """f1: the P1 + Morley assembler on an arbitrary conforming triangulation (L-shaped plate
+    with a hole; shuffled vertex and triangle order, mixed orientation) and the .npz on-disk
+    format of the hot path's inputs."""
+    from plate_inverse_problem_b200 import synthetic as syn
+    plate = syn.make_named("tinyL")
+    rect = syn.make_plate(*syn.SHAPED_SIZES["tinyL"])
+    assert plate.N < rect.N and len(plate.mats) == 26
+    # the same geometry handed over as a raw triangulation: permuted vertices / triangles, every
+    # other triangle clockwise -> same physics (FRF), different numbering
+    m = plate.mesh
+    rng = np.random.default_rng(0)
+    vp = rng.permutation(m.points.shape[0])
+    inv = np.argsort(vp)
+    tris = inv[m.tris][rng.permutation(m.tris.shape[0])]
+    tris[::2] = tris[::2][:, [0, 2, 1]]
+    mesh2 = syn.mesh_from_triangulation(m.points[vp], tris, m.clamped_vertices[vp])
+    plate2 = syn.plate_from_mesh(mesh2, plate.test_point)
+    assert plate2.N == plate.N and mesh2.clamped_edges.sum() == m.clamped_edges.sum()
+    from plate_inverse_problem_b200.Problem import AP1030
+    inertia = orc.inertia_scalars(H, 1600.0, AP1030.mass, AP1030.radius, AP1030.height)
+    tr = orc.make_transform("sol", H, (0, 45, -45, 90))
+    mk = lambda pl: orc.OracleProblem(pl, tr, inertia, AP1030.height, AP1030.effective_height,
+                                      AP1030.transverse_sensitivity)
+    freqs = np.linspace(40.0, 600.0, 5)
+    op1, op2 = mk(plate), mk(plate2)
+    fr1, fr2 = op1.forward(freqs, PARAMS), op2.forward(freqs, PARAMS)
+    assert relerr(fr2, fr1) < 1e-7          # the w-gradient dofs flip sign with the edge orientation; fr cannot
+    assert relerr(fr1, mk(rect).forward(freqs, PARAMS)) > 1e-3      # the cut-outs matter
+    # adjoint gradient against central differences on the shaped plate
+    ref = fr1 * 1.1
+    L, g, _ = op1.loss_and_grad(freqs, PARAMS, ref, "MSE_LOG_AFC")
+    for j in (0, 2, 4):
+        h = 1e-5 * PARAMS[j]
+        p1, p2 = PARAMS.copy(), PARAMS.copy()
+        p1[j] += h
+        p2[j] -= h
+        fd = (orc.loss_value(op1.forward(freqs, p1), ref, "MSE_LOG_AFC")
+              - orc.loss_value(op1.forward(freqs, p2), ref, "MSE_LOG_AFC")) / (2 * h)
+        assert abs(g[j] - fd) <= 1e-4 * abs(fd), j
+    # symbolic analysis copes with the non-convex domain
+    S = _lib.host_symbolic(plate.N, op1.native["indices"], op1.native["indptr"])
+    assert sorted(S["perm"].tolist()) == list(range(plate.N))
+    # on-disk round trip: bit-identical matrices (explicit zeros included) and operators
+    path = os.path.join(tmp_path, "plate.npz")
+    syn.save_plate(path, plate)
+    back = syn.load_plate(path)
+    for a, b in zip(plate.mats, back.mats):
+        assert np.array_equal(a.row, b.row) and np.array_equal(a.col, b.col) and np.array_equal(a.data, b.data)
+    for k in ("rhs_vec", "interp_mat", "interp_mat_Lh", "interp_mat_Wx", "interp_mat_Wy"):
+        assert np.array_equal(getattr(plate, k), getattr(back, k)), k
+    assert back.N == plate.N and np.array_equal(back.mesh.tris, plate.mesh.tris)
+    assert relerr(mk(back).forward(freqs, PARAMS), fr1) == 0.0
+    with pytest.raises(ValueError):
+        syn.mesh_from_triangulation(m.points, np.vstack([m.tris, m.tris[:1], m.tris[:1]]), m.clamped_vertices)
