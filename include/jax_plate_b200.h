@@ -111,6 +111,9 @@ int jpb_get_ordering(const jpb_state* st, int solver_num, int32_t* perm);
  *   4: data[B1,nnz]   b[B0,B1,N]   -> out[B0,B1,N]  (B1 factorisations, B0 rhs each)
  * nbatch0 = B (modes 1-3) or B0 (mode 4); nbatch1 = B1 (mode 4 only).
  * transpose != 0 solves A^T x = b (plain transpose, UMFPACK_Aat, InnerState.h:183-185).
+ * data / b / out (mat / vec / out) may be HOST or DEVICE pointers (unified addressing decides per
+ * copy), which is what lets the XLA-FFI handlers of csrc/xla_ffi.cc pass XLA's device buffers
+ * straight through; `status` is always host memory.
  * status (optional, one int per system): bit 0 (1) zero / non-finite pivot block, bit 1 (2)
  * backward error above the tolerance of jpb_set_residual_tolerance. */
 int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const double* data,

@@ -980,7 +980,7 @@ int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const doub
         const int nw = (int)std::min<int64_t>(W, ms.nsys - i0);
         {
             Span span(st, s, PH_H2D);
-            CK(cudaMemcpyAsync(dat, (const cd*)data + i0 * nnz, (size_t)nw * nnz * 16, cudaMemcpyHostToDevice, s));
+            CK(cudaMemcpyAsync(dat, (const cd*)data + i0 * nnz, (size_t)nw * nnz * 16, cudaMemcpyDefault, s));
         }
         factor(st, s, P, nw, F, dat, false, dstat + i0);
         for (int64_t j0 = 0; j0 < ms.nrhs; j0 += JC) {
@@ -990,13 +990,13 @@ int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const doub
             {
                 Span span(st, s, PH_H2D);
                 if (ms.rhs_sb == 0 && ms.rhs_sj == 0) {          // one shared vector (modes 0, 1)
-                    CK(cudaMemcpyAsync(vb, hb, (size_t)N * 16, cudaMemcpyHostToDevice, s));
+                    CK(cudaMemcpyAsync(vb, hb, (size_t)N * 16, cudaMemcpyDefault, s));
                     sb = 0; sj = 0;
                 } else {
                     for (int j = 0; j < nj; ++j) {
                         const cd* src = hb + ((j0 + j) * ms.rhs_sj + i0 * ms.rhs_sb) * N;
                         CK(cudaMemcpyAsync(vb + (int64_t)j * nw * N, src, (size_t)nw * N * 16,
-                                           cudaMemcpyHostToDevice, s));
+                                           cudaMemcpyDefault, s));
                     }
                     sb = 1; sj = nw;
                     if (ms.rhs_sb == 0) sb = 0;
@@ -1008,7 +1008,7 @@ int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const doub
                 Span span(st, s, PH_D2H);
                 for (int j = 0; j < nj; ++j)
                     CK(cudaMemcpyAsync(hout + ((j0 + j) * ms.nsys + i0) * N, vx + (int64_t)j * nw * N,
-                                       (size_t)nw * N * 16, cudaMemcpyDeviceToHost, s));
+                                       (size_t)nw * N * 16, cudaMemcpyDefault, s));
             }
         }
     }
@@ -1047,23 +1047,23 @@ int jpb_matvec(jpb_state* st, int solver_num, int mode, int transpose, const dou
     cd* hout = (cd*)out;
     for (int64_t i0 = 0; i0 < ms.nsys; i0 += W) {
         const int nw = (int)std::min<int64_t>(W, ms.nsys - i0);
-        CK(cudaMemcpyAsync(dat, (const cd*)mat + i0 * nnz, (size_t)nw * nnz * 16, cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(dat, (const cd*)mat + i0 * nnz, (size_t)nw * nnz * 16, cudaMemcpyDefault, s));
         for (int64_t j0 = 0; j0 < ms.nrhs; j0 += JC) {
             const int nj = (int)std::min<int64_t>(JC, ms.nrhs - j0);
             int64_t sb, sj;
             if (ms.rhs_sb == 0 && ms.rhs_sj == 0) {
-                CK(cudaMemcpyAsync(vb, hv, (size_t)N * 16, cudaMemcpyHostToDevice, s));
+                CK(cudaMemcpyAsync(vb, hv, (size_t)N * 16, cudaMemcpyDefault, s));
                 sb = 0; sj = 0;
             } else {
                 for (int j = 0; j < nj; ++j)
                     CK(cudaMemcpyAsync(vb + (int64_t)j * nw * N, hv + ((j0 + j) * ms.rhs_sj + i0 * ms.rhs_sb) * N,
-                                       (size_t)nw * N * 16, cudaMemcpyHostToDevice, s));
+                                       (size_t)nw * N * 16, cudaMemcpyDefault, s));
                 sb = ms.rhs_sb == 0 ? 0 : 1; sj = nw;
             }
             spmv(st, s, P, transpose != 0, dat, 1, false, vb, sb, sj, nullptr, 0, 0, vx, nw, nj);
             for (int j = 0; j < nj; ++j)
                 CK(cudaMemcpyAsync(hout + ((j0 + j) * ms.nsys + i0) * N, vx + (int64_t)j * nw * N,
-                                   (size_t)nw * N * 16, cudaMemcpyDeviceToHost, s));
+                                   (size_t)nw * N * 16, cudaMemcpyDefault, s));
         }
     }
     CK(cudaStreamSynchronize(s));

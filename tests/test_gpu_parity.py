@@ -735,3 +735,47 @@ def test_inverse_problem_loops_on_the_fused_path(small):
     assert np.max(np.abs(est[[0, 1, 2, 4]] / truth[[0, 1, 2, 4]] - 1.0)) < 2e-2     # nu12 is weakly identifiable
     r = O.optimize_trust_region(loss, x0, N_steps=12, delta_max=0.5, method="gn")
     assert r.f < 1e-2 * f0, (f0, r.f, r.status)
+
+
+def test_solve_and_matvec_accept_device_pointers(state, tiny):
+    """`jpb_solve` / `jpb_matvec` take host or device pointers (unified addressing): what the
+    XLA-FFI handlers of csrc/xla_ffi.cc rely on to pass XLA's device buffers straight through."""
+    import torch
+    from plate_inverse_problem_b200 import _lib
+    num = _register(state, tiny)
+    data, b = REF_TINY["r_data"], REF_TINY["r_b"][0]
+    x_host = state.solve(data, b, num, False, 0, 3)
+    y_host = state.matvec(data, b, num, True, 0, 3)
+    dev = torch.device("cuda", 0)
+    d_data, d_b = torch.from_numpy(data).to(dev), torch.from_numpy(b).to(dev)
+    d_x, d_y = torch.zeros_like(d_b), torch.zeros_like(d_b)
+    torch.cuda.synchronize()
+    st, vp = state._st, _lib.C.c_void_p
+    st.check(st.lib.jpb_solve(st.h, num, 3, 0, vp(d_data.data_ptr()), vp(d_b.data_ptr()), 3, 0, vp(d_x.data_ptr()), None))
+    st.check(st.lib.jpb_matvec(st.h, num, 3, 1, vp(d_data.data_ptr()), vp(d_b.data_ptr()), 3, 0, vp(d_y.data_ptr())))
+    assert np.array_equal(d_x.cpu().numpy(), x_host) and np.array_equal(d_y.cpu().numpy(), y_host)
+
+
+def test_shaped_plate_fused_path_against_oracle():
+    """f1: the fused path on a complex geometry (L-shaped plate with a hole, general
+    triangulation) against the oracle, and on the same plate loaded back from its .npz file."""
+    import tempfile
+    from plate_inverse_problem_b200 import synthetic as syn
+    from plate_inverse_problem_b200.Material import SOL
+    from plate_inverse_problem_b200.Problem import AP1030, Geometry, Problem
+    plate = syn.make_named("smallL")
+    inertia = orc.inertia_scalars(2e-3, 1600.0, AP1030.mass, AP1030.radius, AP1030.height)
+    op = orc.OracleProblem(plate, orc.make_transform("sol", 2e-3, (0, 45, -45, 90)), inertia, AP1030.height,
+                           AP1030.effective_height, AP1030.transverse_sensitivity)
+    with tempfile.TemporaryDirectory() as d:
+        syn.save_plate(os.path.join(d, "p.npz"), plate)
+        plate_disk = syn.load_plate(os.path.join(d, "p.npz"))
+    prob = Problem(Geometry(2e-3, plate_disk), SOL(1600.0, (0, 45, -45, 90), *PARAMS), AP1030)
+    freqs = np.linspace(40.0, 600.0, 9)
+    fr_o = op.forward(freqs, PARAMS)
+    fr = prob.solveForward(freqs)
+    assert float(np.max(np.abs(fr - fr_o) / fr_o)) <= 1e-8
+    ref = fr_o * (1.0 + 0.1 * np.cos(np.arange(freqs.size)))
+    L, g = prob.getLossFunction(freqs, ref, "MSE_LOG_AFC").value_and_grad(PARAMS)
+    L_o, g_o, _ = op.loss_and_grad(freqs, PARAMS, ref, "MSE_LOG_AFC")
+    assert abs(L - L_o) <= TOL_LG * abs(L_o) and relerr(g, g_o) <= TOL_LG
