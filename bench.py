@@ -573,6 +573,65 @@ def north_star(args, world, rank, local, dev, dmma_peak, hbm_peak):
     return out
 
 
+def run_candidates(args):
+    """BASELINE configs[4]: a batch of parameter candidates (default 64) x a frequency sweep
+    (default 500) on the ~5e4-DOF plate, the flattened (candidate, frequency) list sharded over
+    the GPUs, per-candidate losses and gradients from ONE call of the public API
+    (`loss.value_and_grad(params[C, P])` -> `jpb_eval_candidates`), one all-reduce of [C, 1+P]."""
+    import torch
+    import torch.distributed as dist
+    from plate_inverse_problem_b200.Material import SOL
+    from plate_inverse_problem_b200.Problem import AP1030, Geometry, Problem
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    wl = args.workload if args.workload != "cfg1" else "cfg5"
+    C_, F = args.candidates, args.freqs or 500
+    prob = Problem(Geometry(H, make_inputs(wl)), SOL(RHO, ANGLES, *PARAMS), AP1030, device=local)
+    info = prob.symbolic_info()
+    freqs = np.linspace(40.0, 600.0, F)
+    ref = prob.solveForward(freqs, PARAMS * np.array([1.1, 1.1, 1.2, 1.0, 1.5]))
+    loss = prob.getLossFunction(freqs, ref, "MSE_LOG_AFC")
+    cands = PARAMS[None, :] * (1.0 + 0.1 * np.random.default_rng(1234).uniform(-1, 1, (C_, PARAMS.size)))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    for _ in range(max(1, min(args.warmup, 1))):
+        L, g = loss.value_and_grad(cands)
+    steps = max(1, min(args.steps, 3))
+    with ClockSampler(local) as clocks:
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            L, g = loss.value_and_grad(cands)
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    tm = prob.timings()
+    L1, g1 = loss.value_and_grad(cands[3])          # one candidate on its own (all ranks: it is collective)
+    assert abs(L[3] - L1) <= 1e-10 * abs(L1) and np.allclose(g[3], g1, rtol=1e-8, atol=1e-12 * np.abs(g1).max())
+    if rank == 0:
+        v = C_ * F * steps / dt.item()
+        print(json.dumps(dict(
+            metric=METRIC, value=v, unit="evals/s", n_gpus=world, steps=steps, warmup=1, ms_per_step=1e3 * dt.item() / steps,
+            higher_is_better=True, scaling="strong", vs_baseline=None, dtype="c128", data="synthetic",
+            config=dict(workload=workload_name(wl), mode="candidate sweep", candidates=C_, freqs_per_candidate=F,
+                        systems_per_step=C_ * F, N=int(info["N"]), nnz=int(info["nnz"]), systems_per_wave=int(tm["wave"]),
+                        parallelism=f"(candidate, frequency) shard x{world}, one all-reduce of [C, 1+P]"),
+            e2e=dict(value=v, unit="evals/s", note="timed through loss.value_and_grad(params[C, P]) with host buffers"),
+            gpu_launches=int(tm["launches"] * steps), clocks=clocks.summary(),
+            loss_range=[float(L.min()), float(L.max())])))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def st_refine(prob):
     return getattr(prob, "_refinement", 1)
 
@@ -593,9 +652,13 @@ def main():
     ap.add_argument("--no-north-star", action="store_true")
     ap.add_argument("--north-star-freqs", type=int, default=0)
     ap.add_argument("--profile", action="store_true", help="short device-only run (for ncu)")
+    ap.add_argument("--candidates", type=int, default=0,
+                    help="candidate-sweep mode (BASELINE configs[4]): this many parameter candidates x --freqs")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.candidates:
+        run_candidates(args)
     else:
         run_ours(args)
 

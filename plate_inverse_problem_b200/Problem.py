@@ -203,17 +203,22 @@ class Problem:
 
             def local(lo, hi):
                 nloc = hi - lo
-                coef, s, dc, ds = self.coefficients(frequencies[lo:hi], p, with_jacobian=True)
+                coef, s, _, _ = self.coefficients(frequencies[lo:hi], p, with_jacobian=False)
                 coef, s = np.ascontiguousarray(coef), np.ascontiguousarray(s)
                 ref = np.ascontiguousarray(reference_fr[lo:hi])
                 fr, loss_sum = np.zeros(nloc), np.zeros(1)
                 ct = np.zeros((nloc, coef.shape[1]), dtype=np.complex128)
                 cts = np.zeros(nloc, dtype=np.complex128)
                 st = self._st
-                st.check(st.lib.jpb_eval_loss_grad(st.h, self.solver_num, nloc, _lib.ptr(coef), _lib.ptr(s),
-                                                   _lib.ptr(ref), _lib.ptr(self.weights), ltype, F,
-                                                   _lib.ptr(fr), _lib.ptr(loss_sum), _lib.ptr(ct),
-                                                   _lib.ptr(cts), None))
+                # the native call (blocking, GIL released by ctypes) runs on a helper thread while
+                # this one differentiates the material transform: the Jacobians are only needed for
+                # the chain rule after the device has finished
+                fut = _native_pool().submit(
+                    st.lib.jpb_eval_loss_grad, st.h, self.solver_num, nloc, _lib.ptr(coef), _lib.ptr(s),
+                    _lib.ptr(ref), _lib.ptr(self.weights), ltype, F, _lib.ptr(fr), _lib.ptr(loss_sum),
+                    _lib.ptr(ct), _lib.ptr(cts), None)
+                _, _, dc, ds = self.coefficients(frequencies[lo:hi], p, with_jacobian=True)
+                st.check(fut.result())
                 value_and_grad.last_fr = fr
                 # chain rule through the coefficient functions
                 g = np.real(np.einsum("fk,fkp->p", ct, dc) + np.einsum("f,fp->p", cts, ds))
@@ -320,6 +325,18 @@ class Problem:
             Jr = (dr[:, None] * J) * scaling
             return float(np.mean(r ** 2)), 2.0 * (r @ Jr) / n, 2.0 * (Jr.T @ Jr) / n
         return model
+
+
+_POOL = None
+
+
+def _native_pool():
+    """One helper thread for blocking native calls that overlap host-side differentiation."""
+    global _POOL
+    if _POOL is None:
+        from concurrent.futures import ThreadPoolExecutor
+        _POOL = ThreadPoolExecutor(max_workers=1, thread_name_prefix="jpb-native")
+    return _POOL
 
 
 def _real_reference(reference_fr):

@@ -160,6 +160,7 @@ struct jpb_state {
     std::string err;
     int64_t budget = 0;
     int refine = 1;
+    int sm_count = 148;
     int refine_extra = 0;          // adaptive steps on top, only for vectors not yet converged (off by default:
                                    // measured, they do not move the plate systems)
     double refine_tol = 1e-11;     // ... i.e. last correction > refine_tol * ||x|| (max-norms)
@@ -294,6 +295,9 @@ struct Tuning {
     // shared memory, so finer groups mean more resident CTAs for the smaller fronts);
     // CTA width 64 up to order smem_nt64, 128 up to smem_nt128, 256 above
     int smem_step = 4, smem_nt64 = 48, smem_nt128 = 80;
+    // 256-thread class: strip updates and Schur complement through the TMA-fed CTA-level GEMM
+    // (default off: measured slower than the per-warp loops, profiles/r2_summary.md)
+    int tma = 0;
     Tuning() {
         auto geti = [](const char* name, int def) {
             const char* v = getenv(name);
@@ -312,6 +316,7 @@ struct Tuning {
         smem_step = std::max(1, geti("JPB_SMEM_STEP", smem_step));
         smem_nt64 = geti("JPB_SMEM_NT64", smem_nt64);
         smem_nt128 = geti("JPB_SMEM_NT128", smem_nt128);
+        tma = geti("JPB_TMA", tma);
     }
 };
 // symbolic options, overridable for tuning runs (JPB_LEAF, JPB_RELAX_SMALL, ...)
@@ -365,7 +370,11 @@ void factor(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* F, const cd
                 else if (g.nt == 128) { JPB_FACTOR(factor_smem_kernel, 128) }
                 else { JPB_FACTOR(factor_smem_kernel, 64) }
             } else {
-                if (g.nt == 256) { JPB_FACTOR(factor_level_kernel, 256) }
+                if (g.nt == 256 && tuning().tma) {
+                    if (ent_order) factor_level_kernel<true, 256, true><<<grid, 256, GB_SMEM, s>>>(P.sd, lf, nsys, F, data, status);
+                    else factor_level_kernel<false, 256, true><<<grid, 256, GB_SMEM, s>>>(P.sd, lf, nsys, F, data, status);
+                }
+                else if (g.nt == 256) { JPB_FACTOR(factor_level_kernel, 256) }
                 else if (g.nt == 128) { JPB_FACTOR(factor_level_kernel, 128) }
                 else { JPB_FACTOR(factor_level_kernel, 64) }
             }
@@ -540,8 +549,13 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
     int64_t per = (P.S.front_slots + nnz + P.S.vec_slots + 5 * (int64_t)N) * 16 + nchunks * K * 16 + 256;
     int64_t W = std::max<int64_t>(1, std::min<int64_t>(B, budget_bytes(st) / per));
     W = std::min<int64_t>(W, 65535);
-    {   // equal waves: 250 systems with room for 150 run as 125 + 125, not 150 + 100 (the
-        // narrow launches at the top of the elimination tree cost the same for 100 as for 150)
+    {   // Wave shaping.  Near the root of the elimination tree a level holds one or two fronts
+        // per system, i.e. W or 2 W CTAs of the 256-thread class (2 resident per SM): a wave of
+        // 160 systems puts a second CTA on 12 of the 148 SMs and the whole level waits for them,
+        // so a wave that exceeds the SM count is cut to a multiple of it (measured at N = 1e5:
+        // 1.52 ms per system at W = 148 against 1.61 at W = 160).  Then equal waves: 250 systems
+        // with room for 148 run as 125 + 125, not 148 + 102 (the narrow launches cost the same).
+        if (W > st->sm_count && P.S.max_s > 256) W = (W / st->sm_count) * st->sm_count;
         const int64_t nwaves = (B + W - 1) / W;
         W = std::min<int64_t>(W, (((B + nwaves - 1) / nwaves) + 7) & ~(int64_t)7);
     }
@@ -665,6 +679,11 @@ int jpb_create(jpb_state** out, int device) {
     st->device = device;
     if (const char* v = getenv("JPB_STREAMS")) st->nstreams = std::max(1, std::min(16, atoi(v)));
     if (cudaSetDevice(device) != cudaSuccess) return JPB_ECUDA;
+    {
+        int n_sm = 0;
+        if (cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && n_sm > 0)
+            st->sm_count = n_sm;
+    }
     if (cudaStreamCreateWithFlags(&st->stream, cudaStreamNonBlocking) != cudaSuccess) return JPB_ECUDA;
     if (cudaFuncSetAttribute(grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GRAD_SMEM) !=
         cudaSuccess)
@@ -687,6 +706,12 @@ int jpb_create(jpb_state** out, int device) {
         auto setv = [&](auto kernel) {
             ok &= cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) == cudaSuccess;
         };
+        auto setg = [&](auto kernel, int bytes) {
+            ok &= cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) == cudaSuccess;
+        };
+        setg(factor_level_kernel<true, 256, true>, GB_SMEM);
+        setg(factor_level_kernel<false, 256, true>, GB_SMEM);
+        setg(selftest_cta_gemm_kernel, GB_SMEM);
         setv(fwd_level_kernel<false, 256>); setv(fwd_level_kernel<true, 256>);
         setv(bwd_level_kernel<false, 256>); setv(bwd_level_kernel<true, 256>);
         setv(fwd_level_kernel<false, 128>); setv(fwd_level_kernel<true, 128>);
@@ -1383,6 +1408,30 @@ int jpb_selftest(jpb_state* st, double* max_err) {
         worst = std::max(worst, num / den);
     }
     cudaFree(dA); cudaFree(dB); cudaFree(dC); cudaFree(dR);
+    {   // CTA-level GEMM fed by bulk asynchronous copies, against scalar loops
+        const int cases2[][3] = {{64, 64, 16}, {64, 64, 64}, {100, 70, 37}, {130, 200, 5}, {33, 17, 1},
+                                 {256, 192, 203}, {16, 300, 64}, {300, 32, 96}};
+        for (auto& c : cases2) {
+            const int m = c[0], n = c[1], K = c[2], la = K + 3, lb = n + 5, lc = n + 1;
+            std::vector<cd> hA((size_t)m * la), hB((size_t)K * lb), hC((size_t)m * lc);
+            for (auto& v : hA) v = make_double2(rnd(), rnd());
+            for (auto& v : hB) v = make_double2(rnd(), rnd());
+            for (auto& v : hC) v = make_double2(rnd(), rnd());
+            cd *gA = upload(hA), *gB = upload(hB), *gC = upload(hC), *gR = upload(hC);
+            selftest_cta_gemm_kernel<<<1, 256, GB_SMEM, st->stream>>>(gA, la, m, gB, lb, n, K, gC, gR, lc);
+            CK(cudaStreamSynchronize(st->stream));
+            std::vector<cd> oC(hC.size()), oR(hC.size());
+            CK(cudaMemcpy(oC.data(), gC, oC.size() * 16, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(oR.data(), gR, oR.size() * 16, cudaMemcpyDeviceToHost));
+            double num = 0, den = 1e-300;
+            for (size_t i = 0; i < oC.size(); ++i) {
+                num = std::max(num, std::max(std::fabs(oC[i].x - oR[i].x), std::fabs(oC[i].y - oR[i].y)));
+                den = std::max(den, std::max(std::fabs(oR[i].x), std::fabs(oR[i].y)));
+            }
+            worst = std::max(worst, num / den);
+            cudaFree(gA); cudaFree(gB); cudaFree(gC); cudaFree(gR);
+        }
+    }
     *max_err = worst;
     return JPB_OK;
     JPB_CATCH(st)

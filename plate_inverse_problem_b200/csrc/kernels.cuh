@@ -326,6 +326,212 @@ __device__ __forceinline__ void store_tile_cb(const Acc<MB, NB>& acc, cd* C, int
     }
 }
 
+// C -= P for the 16 x 32 warp tile of the CTA-level GEMM: one 8 x 8 accumulator block at a time
+// (a compiler barrier between blocks keeps ptxas from hoisting all 16 read-modify-write loads
+// above the first store, which at 128 registers spilled the accumulators)
+template <int MB, int NB>
+__device__ __forceinline__ void store_tile_sub_blockwise(const Acc<MB, NB>& acc, cd* C, int ldc, int mrows,
+                                                         int ncols, int lane) {
+    const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+    for (int m = 0; m < MB; ++m) {
+        const int i = 8 * m + g;
+#pragma unroll
+        for (int n = 0; n < NB; ++n) {
+            const int j = 8 * n + 2 * t;
+            if (i < mrows && j < ncols) {
+                cd* p = C + (int64_t)i * ldc + j;
+                if (j + 1 < ncols) {
+                    cd v0 = p[0], v1 = p[1];
+                    v0.x -= acc.re[m][n][0]; v0.y -= acc.im[m][n][0];
+                    v1.x -= acc.re[m][n][1]; v1.y -= acc.im[m][n][1];
+                    p[0] = v0; p[1] = v1;
+                } else {
+                    cd v0 = p[0];
+                    v0.x -= acc.re[m][n][0]; v0.y -= acc.im[m][n][0];
+                    p[0] = v0;
+                }
+            }
+            asm volatile("" ::: "memory");
+        }
+    }
+}
+
+// The same epilogue without a second register tile (the 16 x 32 warp tile of the CTA-level
+// GEMM below leaves no room for one): the accumulator is negated in place, the children's
+// entries are added into it, and it is stored.
+template <int MB, int NB>
+__device__ __forceinline__ void store_tile_cb_inplace(Acc<MB, NB>& acc, cd* C, int ldc, int mrows, int ncols,
+                                                      int rc, int cc, const SymDev& sd, const FrontDesc& fd,
+                                                      const ChildInfo* chs, const cd* Fsys, int lane) {
+    const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+    for (int m = 0; m < MB; ++m)
+#pragma unroll
+        for (int n = 0; n < NB; ++n)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) { acc.re[m][n][e] = -acc.re[m][n][e]; acc.im[m][n][e] = -acc.im[m][n][e]; }
+    for (int ci = 0; ci < fd.nchild; ++ci) {
+        ChildInfo ch;
+        if (fd.nchild <= MAXCH) {
+            ch = chs[ci];
+        } else {
+            const FrontDesc fc = sd.fr[sd.children[fd.childptr + ci]];
+            ch.cb = fc.off + (int64_t)fc.k * fc.ld + fc.k;
+            ch.ld = fc.ld;
+            ch.invoff = fc.invoff;
+        }
+        const int* inv = sd.cbinv + ch.invoff;
+        const cd* Fc = Fsys + ch.cb;
+        int ri[MB];
+#pragma unroll
+        for (int m = 0; m < MB; ++m) ri[m] = 8 * m + g < mrows ? __ldg(inv + rc + 8 * m + g) : -1;
+#pragma unroll
+        for (int n = 0; n < NB; ++n)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int cj = 8 * n + 2 * t + e < ncols ? __ldg(inv + cc + 8 * n + 2 * t + e) : -1;
+                if (cj < 0) continue;
+#pragma unroll
+                for (int m = 0; m < MB; ++m)
+                    if (ri[m] >= 0) {
+                        const cd a = Fc[(int64_t)ri[m] * ch.ld + cj];
+                        acc.re[m][n][e] += a.x;
+                        acc.im[m][n][e] += a.y;
+                    }
+            }
+    }
+#pragma unroll
+    for (int m = 0; m < MB; ++m) {
+        const int i = 8 * m + g;
+        if (i >= mrows) continue;
+#pragma unroll
+        for (int n = 0; n < NB; ++n)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int j = 8 * n + 2 * t + e;
+                if (j < ncols) C[(int64_t)i * ldc + j] = make_double2(acc.re[m][n][e], acc.im[m][n][e]);
+            }
+    }
+}
+
+// ------------------------------------------- CTA-level GEMM fed by bulk asynchronous copies
+// C[m x n] (-)= A[m x K] * B[K x n] for the large fronts, all operands row-major in global
+// memory.  The per-warp loops above read every operand element once per warp tile from
+// L1/L2 (4 flop per byte of L1 traffic); here a 256-thread CTA owns a 64 x 64 tile of C, the
+// 64 x 16 panel of A and the 16 x 64 panel of B of a K chunk are brought into shared memory
+// ONCE by the TMA engine (cp.async.bulk, one contiguous row segment per copy, completion on an
+// mbarrier; 16 flop per byte of L2 traffic) while the previous chunk is being multiplied, and
+// the DMMA fragments come from shared memory at ~30 cycles instead of an L2 round trip.
+// Two stages; one __syncthreads per chunk hands the consumed stage back to the producer
+// (warp 0).  Shared leading dimensions (20 and 66 complex) make both fragment loads
+// bank-conflict free.  Warp w computes the 16 x 32 sub-tile (w & 3, w >> 2).
+constexpr int GB_M = 64, GB_N = 64, GB_K = 16;
+constexpr int GB_LDA = GB_K + 4, GB_LDB = GB_N + 2;
+constexpr int GB_STAGE = GB_M * GB_LDA + GB_K * GB_LDB;                  // complex elements per stage
+constexpr int GB_SMEM = 2 * GB_STAGE * (int)sizeof(cd) + 2 * (int)sizeof(uint64_t);
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+struct GemmPipe {
+    cd* buf;            // 2 stages of GB_STAGE complex elements
+    uint64_t* full;     // 2 mbarriers (TMA completion per stage)
+    uint32_t it;        // chunks issued so far by this CTA (stage = it & 1, parity = (it >> 1) & 1)
+};
+
+// epilogue functor: epi(acc, r0, c0, mr, nc, lane) with (r0, c0) the position of the warp's 16 x 32
+// sub-tile inside C and mr x nc its valid extent
+template <class Epi>
+__device__ __noinline__ void cta_gemm(GemmPipe& gp, const cd* A, int lda, int m, const cd* B, int ldb, int n,
+                                         int K, int tid, Epi epi) {
+    const int lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+    const int wr = warp & 3, wc = warp >> 2;
+    const int ntr = (m + GB_M - 1) / GB_M, ntc = (n + GB_N - 1) / GB_N, nch = (K + GB_K - 1) / GB_K;
+    const int NI = ntr * ntc * nch;
+    // global memory written through the generic proxy (the strips of the previous phases) is about
+    // to be read through the async proxy
+    fence_proxy_async();
+    __syncthreads();
+    // One row segment per bulk copy.  UBLKCP is a warp-level instruction with uniform operands:
+    // issued from a lane-strided loop it is serialised lane by lane (80 copies through one warp
+    // cost more than the chunk's DMMAs -- measured, the first version was 1.4x slower than the
+    // per-warp loops); here every warp issues its share (rows warp, warp + 8, ...) from one elected
+    // lane with warp-uniform addresses.
+    auto issue = [&](int item, uint32_t it) {
+        const int tile = item / nch, ch = item - tile * nch;
+        const int R0 = GB_M * (tile % ntr), C0 = GB_N * (tile / ntr), k0 = GB_K * ch;
+        const int kv = min(GB_K, K - k0), nv = min(GB_N, n - C0);
+        cd* As = gp.buf + (it & 1) * GB_STAGE;
+        cd* Bs = As + GB_M * GB_LDA;
+        uint64_t* bar = gp.full + (it & 1);
+        if (tid == 0) mbar_expect_tx(bar, (uint32_t)((GB_M * kv + kv * nv) * sizeof(cd)));
+        if (lane == 0) {
+            for (int r = warp; r < GB_M; r += 8)       // rows past the edge repeat the last valid one
+                bulk_g2s(As + r * GB_LDA, A + (int64_t)min(R0 + r, m - 1) * lda + k0, (uint32_t)(kv * sizeof(cd)), bar);
+            for (int r = warp; r < kv; r += 8)
+                bulk_g2s(Bs + r * GB_LDB, B + (int64_t)(k0 + r) * ldb + C0, (uint32_t)(nv * sizeof(cd)), bar);
+        }
+    };
+    if (NI > 0) issue(0, gp.it);
+    Acc<2, 4> acc;
+    for (int item = 0; item < NI; ++item) {
+        const uint32_t it = gp.it + item;
+        if (item + 1 < NI) issue(item + 1, it + 1);
+        const int tile = item / nch, ch = item - tile * nch;
+        if (ch == 0) acc.zero();
+        mbar_wait(gp.full + (it & 1), (it >> 1) & 1);
+        const cd* As = gp.buf + (it & 1) * GB_STAGE + (16 * wr + g) * GB_LDA + t;
+        const cd* Bs = gp.buf + (it & 1) * GB_STAGE + GB_M * GB_LDA + t * GB_LDB + 32 * wc + g;
+        const int kv = min(GB_K, K - GB_K * ch);
+        const int nfull = kv >> 2, rem = kv & 3;
+#pragma unroll
+        for (int ks = 0; ks < GB_K / 4; ++ks) {
+            if (ks < nfull) {
+                cd a[2], b[4];
+#pragma unroll
+                for (int mi = 0; mi < 2; ++mi) a[mi] = As[8 * mi * GB_LDA + 4 * ks];
+#pragma unroll
+                for (int ni = 0; ni < 4; ++ni) b[ni] = Bs[4 * ks * GB_LDB + 8 * ni];
+                warp_mma_step<2, 4>(acc, a, b);
+            }
+        }
+        if (rem) {      // K tail: both operands masked (stale shared memory beyond the copied part)
+            cd a[2], b[4];
+            const cd zero = make_double2(0.0, 0.0);
+#pragma unroll
+            for (int mi = 0; mi < 2; ++mi) a[mi] = t < rem ? As[8 * mi * GB_LDA + 4 * nfull] : zero;
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) b[ni] = t < rem ? Bs[4 * nfull * GB_LDB + 8 * ni] : zero;
+            warp_mma_step<2, 4>(acc, a, b);
+        }
+        if (ch == nch - 1) {
+            const int r0 = GB_M * (tile % ntr) + 16 * wr, c0 = GB_N * (tile / ntr) + 32 * wc;
+            const int mr = min(16, m - r0), nc = min(32, n - c0);
+            if (mr > 0 && nc > 0) epi(acc, r0, c0, mr, nc, lane);
+        }
+        __syncthreads();      // the stage just read may be refilled (by the issue of item + 2)
+    }
+    gp.it += NI;
+}
+
 // e / d for 0 <= e < 2^24, d >= 1: float reciprocal estimate, corrected to the exact quotient
 // (a few instructions instead of the ~20 of an integer division)
 __device__ __forceinline__ int fast_div(int e, int d, float inv_d) {
@@ -500,11 +706,27 @@ constexpr int KMAX = 32;   // component matrices supported by the fused assembly
 #ifndef JPB_STRIP_WN
 #define JPB_STRIP_WN 2
 #endif
-template <bool ENT_ORDER, int NT>
+//   TMA = true (NT = 256 only): the strip updates of every 64-column super tile and the Schur
+//                  complement run through cta_gemm (operand panels staged in dynamic shared
+//                  memory by bulk asynchronous copies); launch with GB_SMEM dynamic bytes
+template <bool ENT_ORDER, int NT, bool TMA = false>
 __global__ void __launch_bounds__(NT, JPB_OCC / NT)
 factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd* Fall,
                     const cd* __restrict__ data, int* status) {
+    static_assert(!TMA || NT == 256, "the CTA-level GEMM is written for 8 warps");
     __shared__ TileSmem ts;
+    extern __shared__ __align__(16) unsigned char gemm_smem[];
+    GemmPipe gp{nullptr, nullptr, 0u};
+    if (TMA) {
+        gp.buf = reinterpret_cast<cd*>(gemm_smem);
+        gp.full = reinterpret_cast<uint64_t*>(gemm_smem + 2 * GB_STAGE * sizeof(cd));
+        if (threadIdx.x == 0) {
+            mbar_init(gp.full, 1);
+            mbar_init(gp.full + 1, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        // the first __syncthreads below (after the zero fill) publishes the initialised barriers
+    }
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = NT / 32;
     // warp tile: 16 rows x WC columns.  JPB_WN = 0: 16 x 32 for the 256-thread class (operand reuse
@@ -592,7 +814,30 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
         const int j0 = J * TW;
         const int jw = min(TW, k - j0);
         const int j1 = j0 + jw;
-        if (J > 0) {
+        // ks0: first column of the pivot range the warp-level strip update below still has to
+        // apply.  TMA: the range [0, j0s) of the 64-column super tile [j0s, j1s) this pivot tile
+        // belongs to is applied to both tiles at once by the CTA-level GEMM when the super tile
+        // opens; only the other tile of the super tile (32 columns) is left for the warp loops.
+        int ks0 = 0;
+        if (TMA) {
+            const int j0s = j0 & ~(GB_N - 1);
+            ks0 = j0s;
+            if (j0 == j0s && j0s > 0) {
+                const int j1s = min(j0s + GB_N, k);
+                auto sub = [&](cd* C) {
+                    return [=](Acc<2, 4>& acc, int r0, int c0, int mr, int nc, int ln) {
+                        store_tile_sub_blockwise<2, 4>(acc, C + (int64_t)r0 * ld + c0, ld, mr, nc, ln);
+                    };
+                };
+                // column strip rows [j0s, s) x cols [j0s, j1s), then row strip rows [j0s, j1s) x cols [j1s, s)
+                cta_gemm(gp, F + (int64_t)j0s * ld, ld, s - j0s, F + j0s, ld, j1s - j0s, j0s, tid,
+                         sub(F + (int64_t)j0s * ld + j0s));
+                if (s > j1s)
+                    cta_gemm(gp, F + (int64_t)j0s * ld, ld, j1s - j0s, F + j1s, ld, s - j1s, j0s, tid,
+                             sub(F + (int64_t)j0s * ld + j1s));
+            }
+        }
+        if (j0 > ks0) {
             // column strip rows [j0,s) x cols [j0,j1) and row strip rows [j0,j1) x cols [j1,s)
             // warp tiles of 16 x 16 here (SN = 2 accumulator blocks across): with the live state
             // of the tile loop around it the 16 x 32 tile made ptxas spill inside the k-loop
@@ -615,7 +860,8 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
                 Acc<2, SN> acc;
                 acc.zero();
                 prefetch_tile<SN>(F + (int64_t)r * ld + c, ld, mr, nc, lane);
-                warp_gemm<2, SN>(acc, F + (int64_t)r * ld, ld, mr, F + c, ld, nc, j0, lane);
+                warp_gemm<2, SN>(acc, F + (int64_t)r * ld + ks0, ld, mr, F + (int64_t)ks0 * ld + c, ld, nc,
+                                 j0 - ks0, lane);
                 store_tile<2, SN, true>(acc, F + (int64_t)r * ld + c, ld, mr, nc, lane);
             }
             __syncthreads();
@@ -653,7 +899,14 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
     }
     // ---- contribution block: C = sum over children of their blocks (gathered) - Lt * U
     const int m = s - k;
-    if (m > 0) {
+    if (TMA && m > 0) {
+        cd* C = F + (int64_t)k * ld + k;
+        cta_gemm(gp, F + (int64_t)k * ld, ld, m, F + k, ld, m, k, tid,
+                 [&](Acc<2, 4>& acc, int r0, int c0, int mr, int nc, int ln) {
+                     store_tile_cb_inplace<2, 4>(acc, C + (int64_t)r0 * ld + c0, ld, mr, nc, r0, c0, sd, fd, chs,
+                                                 Fsys, ln);
+                 });
+    } else if (m > 0) {
         const int ntr = (m + 15) >> 4, ntc = (m + WC - 1) / WC;
         for (int tile = warp; tile < ntr * ntc; tile += NW) {
             const int rc = 16 * (tile % ntr), cc = WC * (tile / ntr);      // within the block
@@ -1762,6 +2015,37 @@ __global__ void selftest_gemm_kernel(const cd* A, int lda, int mrows, const cd* 
         cd v = make_double2(0.0, 0.0);
         for (int p = 0; p < K; ++p) cfma(v, A[(int64_t)i * lda + p], B[(int64_t)p * ldb + j]);
         Cref[i * 32 + j] = v;
+    }
+}
+
+// cta_gemm against scalar loops: C0 - A B (two back-to-back calls through one pipe, so that the
+// stage / parity bookkeeping across calls is exercised); Cref receives the scalar result
+__global__ void __launch_bounds__(256)
+selftest_cta_gemm_kernel(const cd* A, int lda, int m, const cd* B, int ldb, int n, int K, cd* C, cd* Cref, int ldc) {
+    extern __shared__ __align__(16) unsigned char gemm_smem[];
+    GemmPipe gp{reinterpret_cast<cd*>(gemm_smem), reinterpret_cast<uint64_t*>(gemm_smem + 2 * GB_STAGE * sizeof(cd)), 0u};
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        mbar_init(gp.full, 1);
+        mbar_init(gp.full + 1, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto sub = [=](Acc<2, 4>& acc, int r0, int c0, int mr, int nc, int ln) {
+        store_tile<2, 4, true>(acc, C + (int64_t)r0 * ldc + c0, ldc, mr, nc, ln);
+    };
+    const int K1 = K / 2;
+    if (K1 > 0) cta_gemm(gp, A, lda, m, B, ldb, n, K1, tid, sub);
+    cta_gemm(gp, A + K1, lda, m, B + (int64_t)K1 * ldb, ldb, n, K - K1, tid, sub);
+    for (int e = tid; e < m * n; e += 256) {
+        const int i = e / n, j = e % n;
+        cd v = Cref[(int64_t)i * ldc + j];
+        for (int p = 0; p < K; ++p) {
+            const cd a = A[(int64_t)i * lda + p], b = B[(int64_t)p * ldb + j];
+            v.x -= a.x * b.x - a.y * b.y;
+            v.y -= a.x * b.y + a.y * b.x;
+        }
+        Cref[(int64_t)i * ldc + j] = v;
     }
 }
 
