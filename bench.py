@@ -264,14 +264,14 @@ def committed_factor_traffic(wl, nsys):
     return None, None
 
 
-def whole_step_roofline(info, K, nsys, refine, hbm_gbs, dmma_tf, t_step_ms, wl):
+def whole_step_roofline(info, K, nsys, refine, hbm_gbs, dmma_tf, t_step_ms, wl, residual_pass=1):
     """T_bound = bytes / BW_HBM + flops / FP64 peak per evaluation (phases are
     sequential), fraction = T_bound / T_measured.  nnz(L+U) is guarded by the CPU LU's fill."""
     N, nnz = info["N"], info["nnz"]
     nnz_lu = min(info["nnz_lu"], CPU_FILL.get(wl, info["nnz_lu"]))
     wave = max(1.0, min(nsys, 400.0))
     by = dict(assembly=16 * nnz + K * 8 * nnz / wave, factor_write=16 * nnz_lu, fwd_solve=16 * nnz_lu,
-              adj_solve=16 * nnz_lu, refinement_spmv=2 * refine * 16 * nnz,
+              adj_solve=16 * nnz_lu, refinement_spmv=2 * (refine + residual_pass) * 16 * nnz,
               gradient=K * 8 * nnz / wave + 2 * 16 * N + 8 * nnz / wave, vectors=6 * 16 * N)
     tot = sum(by.values())
     t_bound = tot / (hbm_gbs * 1e9) + info["flops"] / (dmma_tf * 1e12)
@@ -492,7 +492,10 @@ def run_ours(args):
             vs_baseline=None, dtype="c128", data="synthetic",
             config=dict(workload=workload_name(wl), N=int(info["N"]), nnz=int(info["nnz"]),
                         freqs_per_gpu=nloc, freqs_per_step=F_total, params=PARAMS.size,
-                        loss="MSE_LOG_AFC", refinement_steps=refine, parallelism=f"freq-shard x{world}",
+                        loss="MSE_LOG_AFC", refinement_steps=refine,
+                        refinement_policy="one unconditional step per solve (default)" if refine else
+                                          "fast mode: residual pass, a step only for systems above the threshold",
+                        parallelism=f"freq-shard x{world}",
                         systems_per_wave=int(tm["wave"]),
                         l2_policy="working set (fronts of one wave, %.1f GB) far exceeds the 126 MB L2; no flush needed"
                                   % (info["front_slots"] * 16 * min(nloc, tm["wave"]) / 1e9)),
@@ -512,7 +515,7 @@ def run_ours(args):
                                "loops; MEASURED_PEAKS.json holds no FP64 figure",
                           flops_per_system=info["flops"], systems_per_launch_group=int(min(nloc, tm["wave"])),
                           whole_step=whole_step_roofline(info, arm.K, nloc, refine, hbm_peak, dmma_peak,
-                                                         ms_dev / args.steps, wl),
+                                                         ms_dev / args.steps, wl, int(arm.prob._residual_pass)),
                           hbm_peak_source=hbm_src),
             phases_ms=dict(factor=tm["factor_ms"], fwd_solve=tm["fwd_solve_ms"], adj_solve=tm["adj_solve_ms"],
                            spmv=tm["spmv_ms"], grad=tm["grad_ms"], readout=tm["readout_ms"]),
@@ -565,7 +568,8 @@ def north_star(args, world, rank, local, dev, dmma_peak, hbm_peak):
                    roofline=dict(bound="tensor", unit="TFLOP/s", peak=dmma_peak, achieved=fac_tf,
                                  frac=fac_tf / dmma_peak, note="factor phase, all waves of the last step",
                                  whole_step=whole_step_roofline(info, arm.K, nloc, st_refine(arm.prob), hbm_peak,
-                                                                dmma_peak, ms_dev / steps, wl)),
+                                                                dmma_peak, ms_dev / steps, wl,
+                                                                int(arm.prob._residual_pass))),
                    phases_ms=dict(factor=tm["factor_ms"], fwd_solve=tm["fwd_solve_ms"],
                                             adj_solve=tm["adj_solve_ms"], spmv=tm["spmv_ms"], grad=tm["grad_ms"]),
                    cpu_baseline=cb, parity=par)

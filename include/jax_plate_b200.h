@@ -56,9 +56,34 @@ const char* jpb_last_error(const jpb_state* st);
 /* upper bound of device memory (bytes) the state may use for fronts/workspaces;
  * 0 = 80 % of what is free at first use */
 int jpb_set_memory_budget(jpb_state* st, int64_t bytes);
-/* iterative-refinement steps applied after every triangular solve (default 1) */
+/* Iterative refinement of every triangular solve (UMFPACK's Control[UMFPACK_IRSTEP] analogue;
+ * umfpack_zi_solve refines while the backward error improves, at most 2 steps by default):
+ *   jpb_set_refinement(steps)          unconditional steps.  Default 1: the parity-grade setting --
+ *                                      with it the forward error is at or below that of a CPU sparse
+ *                                      LU on the same matrix.
+ *   jpb_set_refinement_threshold(w, t) only used with steps = 0 ("fast mode", +14 % throughput at
+ *                                      N = 2e4): a residual pass over A, then ONE step for exactly the
+ *                                      systems whose normwise backward error
+ *                                      omega = ||b - A x|| / || |A||x| + |b| || is above w (default
+ *                                      1e-15) or whose residual relative to the right-hand side is
+ *                                      above t (default 0 = no such test); w = 0 switches the residual
+ *                                      pass off.  The equilibrated plate systems come out at
+ *                                      omega ~ 1e-16 unrefined, like a CPU sparse LU, and skip the
+ *                                      step; their forward error is then within ~10x of the stand-in
+ *                                      LU's (both are cond(A) * eps). */
 int jpb_set_refinement(jpb_state* st, int steps);
-/* adaptive refinement on top of the unconditional steps: up to `extra_steps` further steps
+int jpb_set_refinement_threshold(jpb_state* st, double omega, double rel_residual);
+/* how many of the vectors solved by the last call took the residual-driven step */
+int jpb_last_refined(jpb_state* st, int64_t* refined, int64_t* solved);
+/* Equilibration (default on; UMFPACK scales rows by default too, Control[UMFPACK_SCALE]): every
+ * system is factorised as S A S with s_i = 2^-floor(log2|a_ii| / 2) -- powers of two, so the
+ * scaled entries are exact -- and right-hand sides / solutions are converted on the way in and
+ * out.  Results are those of the unscaled system up to rounding; what changes is the backward
+ * error of the block factorisation with tile-local pivoting, which for the plate matrices (1e7
+ * between the in-plane and bending blocks) drops to that of a CPU sparse LU in both the plain
+ * and the transposed solve. */
+int jpb_set_equilibration(jpb_state* st, int on);
+/* correction-driven refinement on top of the above: up to `extra_steps` further steps
  * (default 0 = off), each executed only for the systems whose last correction was still larger
  * than tol * ||x|| (max-norms, default 1e-11); the other systems' blocks exit at once.  Meant
  * for matrices on which the static-pivot factorisation has a poor backward error, so that one

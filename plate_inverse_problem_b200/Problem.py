@@ -83,7 +83,8 @@ def union_pattern_and_align(mats, N: int):
 
 class Problem:
     def __init__(self, geometry: Geometry, material: Material, accelerometer: AccelerometerParams,
-                 ref_fr=None, *, cpu: int = 0, device: int = None, refinement: int = 1):
+                 ref_fr=None, *, cpu: int = 0, device: int = None, refinement: int = None,
+                 refinement_threshold=None):
         import os
         self.geometry, self.material, self.accelerometer = geometry, material, accelerometer
         self.reference_fr = ref_fr
@@ -133,8 +134,16 @@ class Problem:
         st.check(st.lib.jpb_add_mat(st.h, N, idx.size, _lib.ptr(idx), _lib.ptr(iptr), _lib.ptr(idxT),
                                     _lib.ptr(iptr), _lib.ptr(permc), idx.dtype.itemsize, _lib.C.byref(num)))
         self.solver_num = num.value
-        st.check(st.lib.jpb_set_refinement(st.h, int(refinement)))
-        self._refinement = int(refinement)
+        # refinement policy (include/jax_plate_b200.h): by default one unconditional step;
+        # refinement=0 is the fast mode (residual pass, a step only for systems that need it)
+        if refinement is not None:
+            st.check(st.lib.jpb_set_refinement(st.h, int(refinement)))
+        if refinement_threshold is not None:       # (omega, relative residual) or omega alone
+            th = np.atleast_1d(np.asarray(refinement_threshold, dtype=np.float64))
+            st.check(st.lib.jpb_set_refinement_threshold(st.h, float(th[0]), float(th[1]) if th.size > 1 else 0.0))
+        self._refinement = 1 if refinement is None else int(refinement)
+        self._residual_pass = self._refinement == 0 and (
+            refinement_threshold is None or float(np.atleast_1d(refinement_threshold)[0]) > 0)
         self.mats = np.ascontiguousarray(self.mats)
         st.check(st.lib.jpb_register_components(st.h, self.solver_num, self.mats.shape[0],
                                                 _lib.ptr(self.mats), _lib.ptr(self.vec), 3,

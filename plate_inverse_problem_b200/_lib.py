@@ -21,7 +21,7 @@ LOSS_TYPES = {"MSE": 0, "RMSE": 1, "MSE_AFC": 2, "MSE_LOG_AFC": 3}
 # every symbol include/jax_plate_b200.h declares
 EXPORTED_SYMBOLS = (
     "jpb_create", "jpb_destroy", "jpb_last_error", "jpb_set_memory_budget", "jpb_set_refinement",
-    "jpb_set_streams", "jpb_set_residual_tolerance", "jpb_set_adaptive_refinement",
+    "jpb_set_streams", "jpb_set_residual_tolerance", "jpb_set_adaptive_refinement", "jpb_set_refinement_threshold", "jpb_last_refined", "jpb_set_equilibration",
     "jpb_add_mat", "jpb_symbolic_info", "jpb_get_ordering", "jpb_solve", "jpb_matvec",
     "jpb_assemble", "jpb_register_components", "jpb_eval_forward", "jpb_eval_loss_grad",
     "jpb_eval_loss_grad_dev", "jpb_eval_candidates", "jpb_eval_candidates_dev", "jpb_eval_jacobian",
@@ -67,6 +67,9 @@ def load_library() -> C.CDLL:
     lib.jpb_eval_jacobian_dev.argtypes = [vp, i32, i64, dp, dp, dp, dp, dp, dp, dp, vp]
     lib.jpb_set_residual_tolerance.argtypes = [vp, C.c_double, C.c_double]
     lib.jpb_set_adaptive_refinement.argtypes = [vp, i32, C.c_double]
+    lib.jpb_set_refinement_threshold.argtypes = [vp, C.c_double, C.c_double]
+    lib.jpb_last_refined.argtypes = [vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    lib.jpb_set_equilibration.argtypes = [vp, i32]
     lib.jpb_last_timings.argtypes = [vp, dp]
     lib.jpb_dmma_peak.argtypes = [vp, dp]
     lib.jpb_selftest.argtypes = [vp, dp]
@@ -126,6 +129,12 @@ class State:
         keys = ("factor_ms", "fwd_solve_ms", "adj_solve_ms", "spmv_ms", "grad_ms", "readout_ms",
                 "h2d_ms", "d2h_ms", "launches", "wave")
         return dict(zip(keys, t.tolist()))
+
+    def refined(self):
+        """(vectors that took the residual-driven refinement step, vectors solved) of the last call."""
+        a, b = C.c_int64(0), C.c_int64(0)
+        self.check(self.lib.jpb_last_refined(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def symbolic_info(self, solver_num: int) -> dict:
         t = np.zeros(10)

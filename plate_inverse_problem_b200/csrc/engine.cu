@@ -127,6 +127,9 @@ struct Pattern {
     // sparse views: CSC (as given) and CSR (rebuilt); *_pos_ent map into front-entry order
     int *d_csc_ptr = nullptr, *d_csc_row = nullptr, *d_csc_col = nullptr, *d_csc_pos_ent = nullptr;
     int *d_csr_ptr = nullptr, *d_csr_col = nullptr, *d_csr_pos = nullptr, *d_csr_pos_ent = nullptr;
+    // equilibration: position of every diagonal entry (CSC order / front-entry order, -1 if absent)
+    // and (row, col) of the entries in front-entry order
+    int *d_diag_csc = nullptr, *d_diag_ent = nullptr, *d_ent_row = nullptr, *d_ent_col = nullptr;
     // registered components
     int K = 0, R = 0;
     double *d_mats = nullptr, *d_mats_f = nullptr, *d_rhs_vec = nullptr, *d_Q = nullptr;
@@ -136,7 +139,8 @@ struct Pattern {
     ~Pattern() {
         void* ptrs[] = {d_fr, d_rowidx_orig, d_children, d_relmap, d_ent_src, d_ent_slot,
                         d_levelfronts, d_cbinv, d_csc_ptr, d_csc_row, d_csc_col, d_csc_pos_ent, d_csr_ptr,
-                        d_csr_col, d_csr_pos, d_csr_pos_ent, d_mats, d_mats_f, d_rhs_vec, d_Q};
+                        d_csr_col, d_csr_pos, d_csr_pos_ent, d_mats, d_mats_f, d_rhs_vec, d_Q,
+                        d_diag_csc, d_diag_ent, d_ent_row, d_ent_col};
         for (void* p : ptrs)
             if (p) cudaFree(p);
     }
@@ -159,7 +163,15 @@ struct jpb_state {
     std::vector<std::unique_ptr<Pattern>> pats;
     std::string err;
     int64_t budget = 0;
+    // refinement policy of every triangular solve: `refine` unconditional steps (default 1); with
+    // refine = 0 a residual pass decides per system whether ONE step runs (backward error above
+    // refine_omega or relative residual above refine_resid), then up to refine_extra
+    // correction-driven steps
     int refine = 1;
+    double refine_omega = 1e-15;
+    double refine_resid = 1e300;   // ... or whose residual relative to the right-hand side is above this (off)
+    unsigned long long* counters = nullptr;      // device: {vectors refined, vectors solved} of the last call
+    int equilibrate = 1;           // symmetric power-of-two diagonal scaling before the factorisation
     int sm_count = 148;
     int refine_extra = 0;          // adaptive steps on top, only for vectors not yet converged (off by default:
                                    // measured, they do not move the plate systems)
@@ -170,7 +182,7 @@ struct jpb_state {
     // refinement step that follows contracts it by ~cond(A) * omega) at no extra pass over A
     double resid_tol = 1e-10, resid_tol0 = 1e-6;
     // workspaces
-    DevBuf F, V, vals, data, vb, vx, vr, vd, vlam, partial, small, hstage, status, norms, lterm, active;
+    DevBuf F, V, vals, data, vb, vx, vr, vd, vlam, partial, small, hstage, status, norms, lterm, active, scal;
     PinBuf pin;
     // instrumentation
     std::vector<TimedSpan> spans;
@@ -194,6 +206,7 @@ struct jpb_state {
         for (auto q : aux) cudaStreamDestroy(q);
         for (auto e : pool) cudaEventDestroy(e);
         if (stream) cudaStreamDestroy(stream);
+        if (counters) cudaFree(counters);
     }
     cudaEvent_t ev() {
         if (pool_used == pool.size()) {
@@ -207,6 +220,7 @@ struct jpb_state {
         spans.clear();
         pool_used = 0;
         launches = 0;
+        if (counters) cudaMemsetAsync(counters, 0, 16, stream);
     }
 };
 
@@ -384,6 +398,29 @@ void factor(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* F, const cd
     }
 }
 
+// equilibration helpers: s from the diagonal of the assembled values, values scaled in place,
+// vectors scaled on the way into / out of the scaled system
+double* equilibrate_values(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* vals, bool ent_order,
+                           double* scal) {
+    if (!st->equilibrate) return nullptr;
+    const int N = P.S.N;
+    const int64_t nnz = P.S.nnz;
+    dim3 g1((N + 255) / 256, nsys);
+    diag_scale_kernel<<<g1, 256, 0, s>>>(N, nnz, ent_order ? P.d_diag_ent : P.d_diag_csc, vals, scal);
+    launch_check(st);
+    dim3 g2((unsigned)((nnz + 255) / 256), nsys);
+    scale_values_kernel<<<g2, 256, 0, s>>>(nnz, N, ent_order ? P.d_ent_row : P.d_csc_row,
+                                           ent_order ? P.d_ent_col : P.d_csc_col, scal, vals);
+    launch_check(st);
+    return scal;
+}
+void scale_vectors(jpb_state* st, cudaStream_t s, Pattern& P, const double* scal, cd* v, int nsys, int nvec) {
+    if (!scal) return;
+    dim3 g((P.S.N + 255) / 256, nvec);
+    scale_vec_kernel<<<g, 256, 0, s>>>(P.S.N, nsys, scal, v);
+    launch_check(st);
+}
+
 // x(b, j) = A_b^-1 rhs(b, j)  (or A_b^-T)
 constexpr int WSOLVE_NW = 8;     // systems (warps) per CTA of the warp-per-system solve kernels
 void tri_solve(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool trans, VecView vv, int phase) {
@@ -472,38 +509,53 @@ void solve_refined(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool 
     VecView vv{rhs, rhs_sb, rhs_sj, x, V, nsys, nrhs, nullptr};
     tri_solve(st, s, P, F, trans, vv, phase);
     const int nvec = nsys * nrhs;
-    // steps 0 .. refine-1 are unconditional; up to refine_extra more run only for the vectors
-    // whose last correction was still above refine_tol * ||x|| (the systems next to a resonance,
-    // where cond(A) * (backward error of the static-pivot factorisation) is not << 1)
-    const int nsteps = st->refine + (st->refine > 0 ? st->refine_extra : 0);
-    int* active = nsteps > st->refine ? (int*)st->active.get((size_t)nvec * sizeof(int)) : nullptr;
-    double* norms = nullptr;
-    if (status && (final_check || st->refine > 0)) norms = (double*)st->norms.get((size_t)nvec * 16);
-    auto flag = [&](double tol) {
-        residual_flag_kernel<<<(nvec + 127) / 128, 128, 0, s>>>(nvec, nsys, norms, tol * tol, status);
-        launch_check(st);
-    };
-    for (int it = 0; it < nsteps; ++it) {
-        const int* act = it >= st->refine ? active : nullptr;
-        // the residual of the unrefined solution doubles as the acceptance test of the fused path
-        double* nrm = (norms && !final_check && it == 0) ? norms : nullptr;
-        if (nrm) CK(cudaMemsetAsync(nrm, 0, (size_t)nvec * 16, s));
+    const int N = P.S.N;
+    double* norms = (double*)st->norms.get((size_t)nvec * 24);
+    auto residual = [&](double* nrm, const int* act) {       // r = rhs - op(A) x  [+ backward-error norms]
+        if (nrm) CK(cudaMemsetAsync(nrm, 0, (size_t)nvec * 24, s));
         spmv(st, s, P, trans, vals, vals_sb, vals_ent_order, x, 1, nsys, rhs, rhs_sb, rhs_sj, r, nsys, nrhs, nrm, act);
-        if (nrm) flag(st->resid_tol0);
+    };
+    auto correct = [&](const int* act) {                     // x += op(A)^-1 r
         VecView v2{r, 1, nsys, d, V, nsys, nrhs, act};
         tri_solve(st, s, P, F, trans, v2, phase);
-        dim3 grid((P.S.N + 255) / 256, nvec);
-        axpy_kernel<<<grid, 256, 0, s>>>(P.S.N, x, d, act);
+        dim3 grid((N + 255) / 256, nvec);
+        axpy_kernel<<<grid, 256, 0, s>>>(N, x, d, act);
         launch_check(st);
-        if (active && it + 1 >= st->refine && it + 1 < nsteps) {
-            refine_active_kernel<<<nvec, 256, 0, s>>>(P.S.N, x, d, st->refine_tol, active, it + 1 == st->refine);
+    };
+    // (1) unconditional steps (jpb_set_refinement; 1 by default).  The residual of the unrefined
+    //     solution doubles as the acceptance test (status bit 2 above resid_tol0): no extra pass.
+    for (int it = 0; it < st->refine; ++it) {
+        const bool test = it == 0 && status && !final_check;
+        residual(test ? norms : nullptr, nullptr);
+        if (test) {
+            residual_flag_kernel<<<(nvec + 127) / 128, 128, 0, s>>>(nvec, nsys, norms, st->resid_tol0 * st->resid_tol0, status);
             launch_check(st);
         }
+        correct(nullptr);
     }
-    if (norms && final_check) {      // ||b - A x|| / ||b|| of what is returned (jpb_solve)
-        CK(cudaMemsetAsync(norms, 0, (size_t)nvec * 16, s));
-        spmv(st, s, P, trans, vals, vals_sb, vals_ent_order, x, 1, nsys, rhs, rhs_sb, rhs_sj, r, nsys, nrhs, norms);
-        flag(st->resid_tol);
+    // (2) without unconditional steps the residual of what we have is the acceptance test and
+    //     decides, per system, whether ONE refinement step runs (jpb_set_refinement_threshold);
+    //     systems that pass leave their blocks at once in the launches of that step
+    if (st->refine == 0 && st->refine_omega > 0.0) {
+        int* active = (int*)st->active.get((size_t)nvec * sizeof(int));
+        residual(norms, nullptr);
+        omega_active_kernel<<<(nvec + 127) / 128, 128, 0, s>>>(
+            nvec, nsys, norms, st->refine_omega * st->refine_omega, st->refine_resid * st->refine_resid,
+            st->resid_tol0 * st->resid_tol0, active, final_check ? nullptr : status, st->counters);
+        launch_check(st);
+        correct(active);
+        // (3) optional correction-driven steps for the systems still moving (jpb_set_adaptive_refinement)
+        for (int e = 0; e < st->refine_extra; ++e) {
+            refine_active_kernel<<<nvec, 256, 0, s>>>(N, x, d, st->refine_tol, active, 0);
+            launch_check(st);
+            residual(nullptr, active);
+            correct(active);
+        }
+    }
+    if (status && final_check) {      // backward error of what is returned (jpb_solve)
+        residual(norms, nullptr);
+        residual_flag_kernel<<<(nvec + 127) / 128, 128, 0, s>>>(nvec, nsys, norms, st->resid_tol * st->resid_tol, status);
+        launch_check(st);
     }
 }
 
@@ -546,7 +598,7 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
     const int K = P.K, R = P.R;
     const int64_t nchunks = (nnz + GRAD_CHUNK - 1) / GRAD_CHUNK;
     // per-system workspace bytes
-    int64_t per = (P.S.front_slots + nnz + P.S.vec_slots + 5 * (int64_t)N) * 16 + nchunks * K * 16 + 256;
+    int64_t per = (P.S.front_slots + nnz + P.S.vec_slots + 5 * (int64_t)N) * 16 + nchunks * K * 16 + 256 + 8 * (int64_t)N;
     int64_t W = std::max<int64_t>(1, std::min<int64_t>(B, budget_bytes(st) / per));
     W = std::min<int64_t>(W, 65535);
     {   // Wave shaping.  Near the root of the elimination tree a level holds one or two fronts
@@ -568,6 +620,7 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
     cd* vr = (cd*)st->vr.get((size_t)W * N * 16);
     cd* vd = (cd*)st->vd.get((size_t)W * N * 16);
     cd* vlam = (cd*)st->vlam.get((size_t)W * N * 16);
+    double* scal_all = (double*)st->scal.get((size_t)W * N * 8);
     cd* partial = adjoint ? (cd*)st->partial.get((size_t)nchunks * W * K * 16) : nullptr;
     // small per-wave array ybar [W,R]; loss terms of the whole batch [B] (summed per segment
     // = per parameter candidate at the end)
@@ -583,18 +636,22 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
         cd* Vc = V + l0 * P.S.vec_slots;
         cd *vbc = vb + l0 * N, *vxc = vx + l0 * N, *vrc = vr + l0 * N, *vdc = vd + l0 * N,
            *vlamc = vlam + l0 * N;
+        const double* scal = nullptr;
         {
             Span span(st, sc, PH_FACTOR);
             assemble_entries(st, sc, P, n, coef + g0 * K, valsc);
+            scal = equilibrate_values(st, sc, P, n, valsc, true, scal_all + l0 * N);
         }
         factor(st, sc, P, n, Fc, valsc, true, status ? status + g0 : nullptr);
         {
             dim3 grid((N + 255) / 256, n);
             scale_rhs_kernel<<<grid, 256, 0, sc>>>(N, P.d_rhs_vec, scale + g0, vbc);
             launch_check(st);
+            scale_vectors(st, sc, P, scal, vbc, n, n);
         }
         solve_refined(st, sc, P, Fc, false, valsc, 1, true, vbc, 1, n, vxc, Vc, vrc, vdc, n, 1, PH_FWD,
                       status ? status + g0 : nullptr, false);
+        scale_vectors(st, sc, P, scal, vxc, n, n);      // back to the caller's units
         {
             Span span(st, sc, PH_READOUT);
             readout_kernel<<<n, 256, 0, sc>>>(N, R, P.d_Q, vxc, y + g0 * R);
@@ -611,9 +668,11 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
             dim3 grid((N + 255) / 256, n);
             cotangent_kernel<<<grid, 256, 0, sc>>>(N, R, P.d_Q, ybar + l0 * R, vbc);
             launch_check(st);
+            scale_vectors(st, sc, P, scal, vbc, n, n);
         }
         solve_refined(st, sc, P, Fc, true, valsc, 1, true, vbc, 1, n, vlamc, Vc, vrc, vdc, n, 1, PH_ADJ,
                       status ? status + g0 : nullptr, false);
+        scale_vectors(st, sc, P, scal, vlamc, n, n);
         {
             Span span(st, sc, PH_GRAD);
             const int ngroups = (n + GRAD_SYS - 1) / GRAD_SYS;
@@ -685,11 +744,12 @@ int jpb_create(jpb_state** out, int device) {
             st->sm_count = n_sm;
     }
     if (cudaStreamCreateWithFlags(&st->stream, cudaStreamNonBlocking) != cudaSuccess) return JPB_ECUDA;
+    if (cudaMalloc(&st->counters, 16) != cudaSuccess || cudaMemset(st->counters, 0, 16) != cudaSuccess) return JPB_ECUDA;
     if (cudaFuncSetAttribute(grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GRAD_SMEM) !=
         cudaSuccess)
         return JPB_ECUDA;
     {
-        const int smem_cap = 112 * smem_ld(112) * (int)sizeof(cd);
+        const int smem_cap = (112 * smem_ld(112) + TW * TW) * (int)sizeof(cd);
         bool ok = true;
         auto set = [&](auto kernel) {
             ok &= cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap) == cudaSuccess;
@@ -749,6 +809,33 @@ int jpb_set_refinement(jpb_state* st, int steps) {
     if (!st || steps < 0 || steps > 8) return fail(st, JPB_EINVAL, "refinement steps must be in [0, 8]");
     st->refine = steps;
     return JPB_OK;
+}
+
+int jpb_set_equilibration(jpb_state* st, int on) {
+    if (!st) return JPB_EINVAL;
+    st->equilibrate = on ? 1 : 0;
+    return JPB_OK;
+}
+
+int jpb_set_refinement_threshold(jpb_state* st, double omega, double rel_residual) {
+    if (!st || !(omega >= 0.0) || !(rel_residual >= 0.0))
+        return fail(st, JPB_EINVAL, "refinement thresholds must be >= 0");
+    st->refine_omega = omega;
+    st->refine_resid = rel_residual > 0.0 ? rel_residual : 1e300;
+    return JPB_OK;
+}
+
+int jpb_last_refined(jpb_state* st, int64_t* refined, int64_t* solved) {
+    JPB_TRY(st)
+    if (!st || !refined || !solved) throw InvalidArg("null argument");
+    CK(cudaSetDevice(st->device));
+    unsigned long long h[2] = {0, 0};
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(h, st->counters, 16, cudaMemcpyDeviceToHost));
+    *refined = (int64_t)h[0];
+    *solved = (int64_t)h[1];
+    return JPB_OK;
+    JPB_CATCH(st)
 }
 
 int jpb_set_adaptive_refinement(jpb_state* st, int extra_steps, double tol) {
@@ -897,6 +984,15 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
                 }
                 P->fgroups[l].back().count++;
             }
+            // shared-memory-resident fronts keep a copy of the pivot tile behind the front for the
+            // Newton-Schulz polish of its inverse: (widest pivot tile of the group)^2 elements
+            for (Pattern::FactorGroup& g : P->fgroups[l]) {
+                if (!g.smem) continue;
+                int wk = 1;
+                for (int q = 0; q < g.count; ++q)
+                    wk = std::max(wk, std::min(TW, S.f_k[S.levelfronts[S.levelptr[l] + g.first + q]]));
+                g.smem += wk * wk * (int)sizeof(cd);
+            }
         }
     }
     // inverse extend-add maps (parent contribution row -> child contribution row) and the
@@ -938,6 +1034,16 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
     P->d_csr_col = upload(csr_col);
     P->d_csr_pos = upload(csr_pos);
     P->d_csr_pos_ent = upload(csr_pos_ent);
+    {
+        std::vector<int> diag_csc(N, -1), diag_ent(N, -1), ent_row(nnz), ent_col(nnz);
+        for (int64_t e = 0; e < nnz; ++e)
+            if (csc_row[e] == csc_col[e]) { diag_csc[csc_col[e]] = (int)e; diag_ent[csc_col[e]] = entpos[e]; }
+        for (int64_t q = 0; q < nnz; ++q) { ent_row[q] = csc_row[S.ent_src[q]]; ent_col[q] = csc_col[S.ent_src[q]]; }
+        P->d_diag_csc = upload(diag_csc);
+        P->d_diag_ent = upload(diag_ent);
+        P->d_ent_row = upload(ent_row);
+        P->d_ent_col = upload(ent_col);
+    }
     P->sd = SymDev{P->d_fr, P->d_rowidx_orig, P->d_children, P->d_relmap, P->d_ent_src, P->d_ent_slot, P->d_cbinv,
                    S.front_slots, S.vec_slots, S.nnz, S.N};
     // the dynamic shared memory of the solve kernels holds one front-local vector
@@ -986,7 +1092,7 @@ int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const doub
     const bool trans = transpose != 0;
     // rhs chunk: bound the front-local vector workspace
     const int64_t JC = std::min<int64_t>(ms.nrhs, 64);
-    int64_t per = (P.S.front_slots + nnz) * 16 + JC * (P.S.vec_slots + 4 * (int64_t)N) * 16 + 64;
+    int64_t per = (P.S.front_slots + nnz) * 16 + JC * (P.S.vec_slots + 4 * (int64_t)N) * 16 + 64 + 8 * (int64_t)N;
     int64_t W = std::max<int64_t>(1, std::min<int64_t>(ms.nsys, budget_bytes(st) / per));
     while (W * JC > 65535) --W;
     st->wave = (double)W;
@@ -997,6 +1103,7 @@ int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const doub
     cd* vx = (cd*)st->vx.get((size_t)W * JC * N * 16);
     cd* vr = (cd*)st->vr.get((size_t)W * JC * N * 16);
     cd* vd = (cd*)st->vd.get((size_t)W * JC * N * 16);
+    double* scal_buf = (double*)st->scal.get((size_t)W * N * 8);
     int* dstat = (int*)st->status.get((size_t)ms.nsys * sizeof(int));
     CK(cudaMemsetAsync(dstat, 0, (size_t)ms.nsys * sizeof(int), s));
     const cd* hb = (const cd*)b;
@@ -1007,6 +1114,7 @@ int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const doub
             Span span(st, s, PH_H2D);
             CK(cudaMemcpyAsync(dat, (const cd*)data + i0 * nnz, (size_t)nw * nnz * 16, cudaMemcpyDefault, s));
         }
+        const double* scal = equilibrate_values(st, s, P, nw, dat, false, scal_buf);
         factor(st, s, P, nw, F, dat, false, dstat + i0);
         for (int64_t j0 = 0; j0 < ms.nrhs; j0 += JC) {
             const int nj = (int)std::min<int64_t>(JC, ms.nrhs - j0);
@@ -1014,9 +1122,16 @@ int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const doub
             int64_t sb, sj;
             {
                 Span span(st, s, PH_H2D);
-                if (ms.rhs_sb == 0 && ms.rhs_sj == 0) {          // one shared vector (modes 0, 1)
+                if (ms.rhs_sb == 0 && ms.rhs_sj == 0 && !scal) {          // one shared vector (modes 0, 1)
                     CK(cudaMemcpyAsync(vb, hb, (size_t)N * 16, cudaMemcpyDefault, s));
                     sb = 0; sj = 0;
+                } else if (ms.rhs_sb == 0 && ms.rhs_sj == 0) {
+                    // ... which every system sees in its own scaled units: one copy per system
+                    CK(cudaMemcpyAsync(vr, hb, (size_t)N * 16, cudaMemcpyDefault, s));
+                    dim3 g((N + 255) / 256, nw);
+                    broadcast_vec_kernel<<<g, 256, 0, s>>>(N, vr, vb);
+                    launch_check(st);
+                    sb = 1; sj = nw;
                 } else {
                     for (int j = 0; j < nj; ++j) {
                         const cd* src = hb + ((j0 + j) * ms.rhs_sj + i0 * ms.rhs_sb) * N;
@@ -1027,8 +1142,10 @@ int jpb_solve(jpb_state* st, int solver_num, int mode, int transpose, const doub
                     if (ms.rhs_sb == 0) sb = 0;
                 }
             }
+            scale_vectors(st, s, P, scal, vb, nw, nw * nj);
             solve_refined(st, s, P, F, trans, dat, 1, false, vb, sb, sj, vx, V, vr, vd, nw, nj,
                           trans ? PH_ADJ : PH_FWD, dstat + i0, true);
+            scale_vectors(st, s, P, scal, vx, nw, nw * nj);
             {
                 Span span(st, s, PH_D2H);
                 for (int j = 0; j < nj; ++j)

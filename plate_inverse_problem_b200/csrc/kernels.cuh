@@ -689,6 +689,48 @@ __device__ __forceinline__ int invert_tile(TileSmem& ts, int n, int tid) {
     return cur;
 }
 
+// Compile-time option (off): measured, the polish costs 14 % of the factor phase at N = 2e4, and
+// with the equilibration of the system (diag_scale_kernel) the plain Gauss-Jordan inverse is
+// already good enough on both sides, see profiles/r2_summary.md.
+#ifndef JPB_NEWTON
+#define JPB_NEWTON 0
+#endif
+// One Newton-Schulz step X <- X + X (I - D X) on the inverted pivot tile.  Gauss-Jordan with
+// partial pivoting leaves a good LEFT residual (X D - I, what Lt = F21 X and the transposed
+// solves see) but a RIGHT residual (D X - I, what the application v_J = X t of the plain solves
+// sees) ~40x above LAPACK's getri -- measured with a numpy replay of the schedule
+// (profiles/r2_summary.md): that alone made the unrefined residual of a solve 50-100x the
+// stand-in LU's and forced an unconditional refinement step (two more sweeps over L and U per
+// solve).  The step squares both residuals; it costs 2 n^3 of the tile, ~10 % of the inversion.
+// X: n x n inverse (leading dimension ldx), W: n x n scratch holding the ORIGINAL tile D on
+// entry (leading dimension ldw, destroyed).  Both in shared memory.  A warp owns whole rows, so
+// both products are formed in place; the caller synchronises the CTA before and after.
+template <int NW>
+__device__ __forceinline__ void newton_polish_tile(cd* X, int ldx, cd* W, int ldw, int n, int warp, int lane) {
+    const int j = min(lane, n - 1);
+    // W <- I - D X   (row i of W depends on row i of D only)
+    for (int i = warp; i < n; i += NW) {
+        cd acc = make_double2(i == j ? 1.0 : 0.0, 0.0);
+#pragma unroll 4
+        for (int p = 0; p < n; ++p) {
+            const cd a = W[i * ldw + p], b = X[p * ldx + j];
+            acc.x = fma(-a.x, b.x, acc.x); acc.x = fma(a.y, b.y, acc.x);
+            acc.y = fma(-a.x, b.y, acc.y); acc.y = fma(-a.y, b.x, acc.y);
+        }
+        __syncwarp();
+        if (lane < n) W[i * ldw + lane] = acc;
+    }
+    __syncthreads();
+    // X <- X + X W   (row i of the result depends on row i of X only)
+    for (int i = warp; i < n; i += NW) {
+        cd acc = X[i * ldx + j];
+#pragma unroll 4
+        for (int p = 0; p < n; ++p) cfma(acc, X[i * ldx + p], W[p * ldw + j]);
+        __syncwarp();
+        if (lane < n) X[i * ldx + lane] = acc;
+    }
+}
+
 // ------------------------------------------------------------------- numeric factorisation
 constexpr int KMAX = 32;   // component matrices supported by the fused assembly
 
@@ -872,6 +914,15 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
         }
         __syncthreads();
         const int cur = invert_tile<NT>(ts, jw, tid);
+        if (JPB_NEWTON && !ts.sing) {      // uniform; the front still holds the original tile (written back below)
+            for (int e = tid; e < jw * TW; e += FACTOR_THREADS) {
+                int i = e >> 5, j = e & 31;
+                if (j < jw) ts.D[cur ^ 1][i][j] = F[(int64_t)(j0 + i) * ld + j0 + j];
+            }
+            __syncthreads();
+            newton_polish_tile<NW>(&ts.D[cur][0][0], TLD, &ts.D[cur ^ 1][0][0], TLD, jw, warp, lane);
+            __syncthreads();
+        }
         const cd (*Dinv)[TLD] = ts.D[cur];
         for (int e = tid; e < jw * TW; e += FACTOR_THREADS) {
             int i = e >> 5, j = e & 31;
@@ -1140,7 +1191,14 @@ factor_smem_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd
             }
             __syncthreads();
         }
-        invert_tile_inplace<NT>(Fs + j0 * lds + j0, lds, jw, tid, ps);
+        cd* Wt = Fs + s * lds;      // jw x jw scratch behind the front (sized by the host per launch group)
+        if (JPB_NEWTON)
+            for (int e = tid; e < jw * jw; e += NT) Wt[e] = Fs[(j0 + e / jw) * lds + j0 + e % jw];
+        invert_tile_inplace<NT>(Fs + j0 * lds + j0, lds, jw, tid, ps);      // starts and ends with a CTA barrier
+        if (JPB_NEWTON && !ps.sing) {
+            newton_polish_tile<NW>(Fs + j0 * lds + j0, lds, Wt, jw, jw, warp, lane);
+            __syncthreads();
+        }
         const int nlt = (s - j1 + 15) >> 4;
         for (int tile = warp; tile < nlt; tile += NW) {
             int r = j1 + 16 * tile, mr = min(16, s - r);
@@ -1609,7 +1667,7 @@ __global__ void spmv_kernel(int N, int64_t nnz, const int* __restrict__ ptr,
     const int b = blockIdx.y % nsys, j = blockIdx.y / nsys;
     // residual check: |r_i|^2 and t_i^2 with t_i = sum_e |a_e| |x_e| + |rhs_i| (1-norm moduli),
     // i.e. the ingredients of the normwise backward error ||r|| / || |A||x| + |b| ||
-    double nr = 0.0, nb2 = 0.0, tacc = 0.0;
+    double nr = 0.0, nb2 = 0.0, nbb = 0.0, tacc = 0.0;
     auto m1 = [](cd v) { return fabs(v.x) + fabs(v.y); };
     if (i < N) {
     const cd* vb = vals + (int64_t)b * vals_sb * nnz;
@@ -1660,35 +1718,41 @@ __global__ void spmv_kernel(int N, int64_t nnz, const int* __restrict__ ptr,
         acc.y = r.y - acc.y;
         if (NORMS) {
             nr = acc.x * acc.x + acc.y * acc.y;
+            nbb = r.x * r.x + r.y * r.y;
             tacc += m1(r);
             nb2 = tacc * tacc;
         }
     }
     yb[i] = acc;
     }
-    // norms[(j * nsys + b) * 2 + {0, 1}] += sum_i {|r_i|^2, t_i^2}: feeds the per-system
-    // residual check (status bit 2); the summation order is irrelevant for a threshold test
+    // norms[(j * nsys + b) * 3 + {0, 1, 2}] += sum_i {|r_i|^2, t_i^2, |rhs_i|^2}: feeds the per-system
+    // residual tests (refinement decision, status bit 2); the summation order is irrelevant for
+    // a threshold test
     if (NORMS) {
-        __shared__ double red[2][32];
+        __shared__ double red[3][32];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             nr += __shfl_xor_sync(0xffffffffu, nr, o);
             nb2 += __shfl_xor_sync(0xffffffffu, nb2, o);
+            nbb += __shfl_xor_sync(0xffffffffu, nbb, o);
         }
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-        if (lane == 0) { red[0][warp] = nr; red[1][warp] = nb2; }
+        if (lane == 0) { red[0][warp] = nr; red[1][warp] = nb2; red[2][warp] = nbb; }
         __syncthreads();
         if (warp == 0) {
             const int nw = blockDim.x >> 5;
-            double a = lane < nw ? red[0][lane] : 0.0, c = lane < nw ? red[1][lane] : 0.0;
+            double a = lane < nw ? red[0][lane] : 0.0, c = lane < nw ? red[1][lane] : 0.0,
+                   e = lane < nw ? red[2][lane] : 0.0;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 a += __shfl_xor_sync(0xffffffffu, a, o);
                 c += __shfl_xor_sync(0xffffffffu, c, o);
+                e += __shfl_xor_sync(0xffffffffu, e, o);
             }
             if (lane == 0) {
-                atomicAdd(norms + 2 * (int64_t)blockIdx.y, a);
-                atomicAdd(norms + 2 * (int64_t)blockIdx.y + 1, c);
+                atomicAdd(norms + 3 * (int64_t)blockIdx.y, a);
+                atomicAdd(norms + 3 * (int64_t)blockIdx.y + 1, c);
+                atomicAdd(norms + 3 * (int64_t)blockIdx.y + 2, e);
             }
         }
     }
@@ -1699,8 +1763,81 @@ __global__ void residual_flag_kernel(int nvec, int nsys, const double* __restric
                                      int* status) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= nvec) return;
-    const double nr = norms[2 * v], nb = norms[2 * v + 1];
+    const double nr = norms[3 * v], nb = norms[3 * v + 1];
     if (!(nr <= tol2 * nb) && !(nr == 0.0)) atomicOr(status + v % nsys, 2);
+}
+
+// Residual-driven refinement: a vector gets a refinement step (active[v] = 1) when its normwise
+// backward error omega_v exceeds refine_omega OR its residual relative to the right-hand side,
+// ||r|| / ||b||, exceeds refine_resid (the systems next to a resonance, where the solution is
+// amplified by 1e3 ... 1e6 and the same backward error leaves a larger residual);
+// status[v % nsys] |= 2 where omega_v > tol0 or is not finite (a step is not expected to rescue
+// that).  norms[3 v + {0, 1, 2}] = ||r||^2, || |A||x| + |b| ||^2, ||b||^2.  counters[0] counts the
+// refined vectors, counters[1] all of them (instrumentation).
+__global__ void omega_active_kernel(int nvec, int nsys, const double* __restrict__ norms, double ro2, double rr2,
+                                    double tol2, int* active, int* status, unsigned long long* counters) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nvec) return;
+    const double nr = norms[3 * v], nb = norms[3 * v + 1], nbb = norms[3 * v + 2];
+    const bool finite = (nr == nr) && (nb == nb) && nr < 1e300 && nb < 1e300;
+    const int act = (finite && (nr > ro2 * nb || nr > rr2 * nbb)) ? 1 : 0;
+    active[v] = act;
+    if (counters) {
+        if (act) atomicAdd(counters, 1ull);
+        atomicAdd(counters + 1, 1ull);
+    }
+    if (status && !(nr <= tol2 * nb) && !(nr == 0.0)) atomicOr(status + v % nsys, 2);
+}
+
+// ------------------------------------------------------------------------- equilibration
+// Symmetric diagonal scaling A~ = S A S with s_i = 2^-floor(log2|a_ii| / 2): a power of two, so
+// the scaled entries are exact and the scaled system is the same problem in other units.  It
+// removes the 1e7 spread between the in-plane and the bending blocks of the plate matrices
+// from the pivot tiles; with it the block factorisation with tile-local pivoting reaches the
+// backward error of a CPU sparse LU in BOTH the plain and the transposed solve without a
+// refinement step (unscaled: 10-40x larger residual in the transposed solve; measured with the
+// numpy replay of the schedule, profiles/r2_summary.md).  s = 1 where the diagonal entry is
+// absent, zero or not finite.
+__global__ void diag_scale_kernel(int N, int64_t nnz, const int* __restrict__ diagpos,
+                                  const cd* __restrict__ vals, double* s) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const int b = blockIdx.y;
+    double out = 1.0;
+    const int q = diagpos[i];
+    if (q >= 0) {
+        const cd d = vals[(int64_t)b * nnz + q];
+        const double m = fmax(fabs(d.x), fabs(d.y));
+        if (m > 0.0 && m < 1e300) out = scalbn(1.0, -(ilogb(m) >> 1));
+    }
+    s[(int64_t)b * N + i] = out;
+}
+// vals[b, q] *= s[b, row q] * s[b, col q]
+__global__ void scale_values_kernel(int64_t nnz, int N, const int* __restrict__ row, const int* __restrict__ col,
+                                    const double* __restrict__ s, cd* vals) {
+    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nnz) return;
+    const int b = blockIdx.y;
+    const double* sb = s + (int64_t)b * N;
+    const double f = sb[row[q]] * sb[col[q]];
+    cd v = vals[(int64_t)b * nnz + q];
+    v.x *= f; v.y *= f;
+    vals[(int64_t)b * nnz + q] = v;
+}
+// v[vec, i] *= s[vec % nsys, i]
+__global__ void scale_vec_kernel(int N, int nsys, const double* __restrict__ s, cd* v) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const int vec = blockIdx.y;
+    const double f = s[(int64_t)(vec % nsys) * N + i];
+    cd a = v[(int64_t)vec * N + i];
+    a.x *= f; a.y *= f;
+    v[(int64_t)vec * N + i] = a;
+}
+// dst[vec, i] = src[i]
+__global__ void broadcast_vec_kernel(int N, const cd* __restrict__ src, cd* dst) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) dst[(int64_t)blockIdx.y * N + i] = src[i];
 }
 
 // x += d  (vector v = blockIdx.y; skipped when inactive)
