@@ -133,6 +133,7 @@ struct Pattern {
     // registered components
     int K = 0, R = 0;
     double *d_mats = nullptr, *d_mats_f = nullptr, *d_rhs_vec = nullptr, *d_Q = nullptr;
+    double* d_mats_diag = nullptr;     // [K][N] diagonals of the component matrices (equilibration)
     SymDev sd{};
     int max_s = 0;
 
@@ -140,7 +141,7 @@ struct Pattern {
         void* ptrs[] = {d_fr, d_rowidx_orig, d_children, d_relmap, d_ent_src, d_ent_slot,
                         d_levelfronts, d_cbinv, d_csc_ptr, d_csc_row, d_csc_col, d_csc_pos_ent, d_csr_ptr,
                         d_csr_col, d_csr_pos, d_csr_pos_ent, d_mats, d_mats_f, d_rhs_vec, d_Q,
-                        d_diag_csc, d_diag_ent, d_ent_row, d_ent_col};
+                        d_diag_csc, d_diag_ent, d_ent_row, d_ent_col, d_mats_diag};
         for (void* p : ptrs)
             if (p) cudaFree(p);
     }
@@ -357,11 +358,24 @@ const Tuning& tuning() {
 // K1: vals[b, q] = sum_k coef[b, k] * mats_f[k, q]  (front-entry order), mats read once per
 // slice of ASM_BCHUNK systems
 constexpr int ASM_BCHUNK = 32;
-void assemble_entries(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, const cd* coef, cd* vals) {
+// With `scal` (equilibration on) the factors s come from the assembled diagonal first and the
+// entries leave the assembly already scaled.  Returns scal or nullptr.
+const double* assemble_entries(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, const cd* coef, cd* vals,
+                               double* scal) {
     dim3 grid((unsigned)((P.S.nnz + 255) / 256), (unsigned)((nsys + ASM_BCHUNK - 1) / ASM_BCHUNK));
+    if (st->equilibrate && scal) {
+        dim3 g1((P.S.N + 255) / 256, nsys);
+        diag_scale_coef_kernel<KMAX><<<g1, 256, 0, s>>>(P.S.N, P.K, P.d_mats_diag, coef, scal);
+        launch_check(st);
+        assemble_kernel<KMAX, true><<<grid, 256, (size_t)ASM_BCHUNK * P.K * 16, s>>>(
+            P.S.nnz, P.K, nsys, P.d_mats_f, coef, vals, ASM_BCHUNK, P.d_ent_row, P.d_ent_col, scal, P.S.N);
+        launch_check(st);
+        return scal;
+    }
     assemble_kernel<KMAX><<<grid, 256, (size_t)ASM_BCHUNK * P.K * 16, s>>>(P.S.nnz, P.K, nsys, P.d_mats_f, coef,
                                                                          vals, ASM_BCHUNK);
     launch_check(st);
+    return nullptr;
 }
 
 // numeric factorisation of `nsys` systems into F.  ent_order: `data` is [nsys, nnz] in
@@ -639,8 +653,7 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
         const double* scal = nullptr;
         {
             Span span(st, sc, PH_FACTOR);
-            assemble_entries(st, sc, P, n, coef + g0 * K, valsc);
-            scal = equilibrate_values(st, sc, P, n, valsc, true, scal_all + l0 * N);
+            scal = assemble_entries(st, sc, P, n, coef + g0 * K, valsc, scal_all + l0 * N);
         }
         factor(st, sc, P, n, Fc, valsc, true, status ? status + g0 : nullptr);
         {
@@ -1251,7 +1264,7 @@ int jpb_register_components(jpb_state* st, int solver_num, int K, const double* 
     CK(cudaSetDevice(st->device));
     const int64_t nnz = P.S.nnz;
     const int N = P.S.N;
-    for (double** p : {&P.d_mats, &P.d_mats_f, &P.d_rhs_vec, &P.d_Q})
+    for (double** p : {&P.d_mats, &P.d_mats_f, &P.d_rhs_vec, &P.d_Q, &P.d_mats_diag})
         if (*p) { cudaFree(*p); *p = nullptr; }
     P.K = 0;
     CK(cudaMalloc(&P.d_mats, (size_t)K * nnz * 8));
@@ -1263,6 +1276,16 @@ int jpb_register_components(jpb_state* st, int solver_num, int K, const double* 
     for (int k = 0; k < K; ++k)
         for (int64_t q = 0; q < nnz; ++q) mf[(size_t)k * nnz + q] = mats[(size_t)k * nnz + P.S.ent_src[q]];
     CK(cudaMemcpy(P.d_mats_f, mf.data(), (size_t)K * nnz * 8, cudaMemcpyHostToDevice));
+    {
+        std::vector<int> diag_csc(N, -1);
+        CK(cudaMemcpy(diag_csc.data(), P.d_diag_csc, (size_t)N * sizeof(int), cudaMemcpyDeviceToHost));
+        std::vector<double> md((size_t)K * N, 0.0);
+        for (int k = 0; k < K; ++k)
+            for (int i = 0; i < N; ++i)
+                if (diag_csc[i] >= 0) md[(size_t)k * N + i] = mats[(size_t)k * nnz + diag_csc[i]];
+        CK(cudaMalloc(&P.d_mats_diag, (size_t)K * N * 8));
+        CK(cudaMemcpy(P.d_mats_diag, md.data(), (size_t)K * N * 8, cudaMemcpyHostToDevice));
+    }
     CK(cudaMemcpy(P.d_rhs_vec, rhs_vec, (size_t)N * 8, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(P.d_Q, Q, (size_t)R * N * 8, cudaMemcpyHostToDevice));
     P.K = K;

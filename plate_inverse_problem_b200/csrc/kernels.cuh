@@ -1882,9 +1882,14 @@ __global__ void refine_active_kernel(int N, const cd* __restrict__ x, const cd* 
 // data[b, e] = sum_k coef[b,k] * mats[k,e]   (K1; HBM-bound: reads K*8 B, writes 16 B per entry)
 // Each thread keeps one entry of all K matrices in registers and loops over the systems of
 // its batch slice, so mats is read once per slice.
-template <int KK>
+// SCALE: the equilibration factors s[b, row e] * s[b, col e] (powers of two, from
+// diag_scale_coef_kernel) are applied as the entry is formed, so the scaled matrix costs no
+// extra pass over the values.
+template <int KK, bool SCALE = false>
 __global__ void assemble_kernel(int64_t nnz, int K, int B, const double* __restrict__ mats,
-                                const cd* __restrict__ coef, cd* data, int bchunk) {
+                                const cd* __restrict__ coef, cd* data, int bchunk,
+                                const int* __restrict__ row = nullptr, const int* __restrict__ col = nullptr,
+                                const double* __restrict__ scal = nullptr, int N = 0) {
     extern __shared__ cd csh[];   // [bchunk][K]
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int b0 = blockIdx.y * bchunk;
@@ -1895,6 +1900,8 @@ __global__ void assemble_kernel(int64_t nnz, int K, int B, const double* __restr
     double m[KK];
 #pragma unroll
     for (int kk = 0; kk < KK; ++kk) m[kk] = kk < K ? mats[(int64_t)kk * nnz + e] : 0.0;
+    int er = 0, ec = 0;
+    if (SCALE) { er = row[e]; ec = col[e]; }
     for (int bb = 0; bb < nb; ++bb) {
         cd v = make_double2(0.0, 0.0);
 #pragma unroll
@@ -1905,8 +1912,35 @@ __global__ void assemble_kernel(int64_t nnz, int K, int B, const double* __restr
                 v.y = fma(c.y, m[kk], v.y);
             }
         }
+        if (SCALE) {
+            const double* sb = scal + (int64_t)(b0 + bb) * N;
+            const double f = sb[er] * sb[ec];
+            v.x *= f; v.y *= f;
+        }
         data[(int64_t)(b0 + bb) * nnz + e] = v;
     }
+}
+
+// s[b, i] of the equilibration from the diagonal of A_b = sum_k coef[b, k] M_k, formed from the
+// K diagonals of the component matrices (mats_diag [K][N], extracted at registration) -- same
+// exponent rule as diag_scale_kernel
+template <int KK>
+__global__ void diag_scale_coef_kernel(int N, int K, const double* __restrict__ mats_diag,
+                                       const cd* __restrict__ coef, double* s) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const int b = blockIdx.y;
+    cd v = make_double2(0.0, 0.0);
+#pragma unroll
+    for (int kk = 0; kk < KK; ++kk)
+        if (kk < K) {
+            const cd c = coef[(int64_t)b * K + kk];
+            const double m = mats_diag[(int64_t)kk * N + i];
+            v.x = fma(c.x, m, v.x);
+            v.y = fma(c.y, m, v.y);
+        }
+    const double mm = fmax(fabs(v.x), fabs(v.y));
+    s[(int64_t)b * N + i] = (mm > 0.0 && mm < 1e300) ? scalbn(1.0, -(ilogb(mm) >> 1)) : 1.0;
 }
 
 // ------------------------------------------------------------------- read-out / loss / grad
