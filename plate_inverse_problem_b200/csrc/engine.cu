@@ -112,10 +112,13 @@ struct Pattern {
     // launch groups of the numeric factorisation, per level: a run of the (size-sorted)
     // front list handled by one kernel instantiation
     struct FactorGroup {
-        int first, count;   // into the level's front list
-        int smem;           // 0: front stays in global memory; else dynamic shared bytes
+        int first, count;   // into the level's FACTOR front list (d_flf + flevelptr[l])
+        int smem;           // dynamic shared bytes (0 for the global-memory kernel)
         int nt;
+        int kind;           // 0: factor_level_kernel, 1: factor_smem_kernel, 2: factor_panel_kernel
     };
+    std::vector<int> flevelptr;
+    int* d_flf = nullptr;
     std::vector<std::vector<FactorGroup>> fgroups;
     // triangular solves: per level {#fronts above wsolve_max (CTA per front), order of the
     // largest remaining front (one warp per system)}
@@ -141,7 +144,7 @@ struct Pattern {
         void* ptrs[] = {d_fr, d_rowidx_orig, d_children, d_relmap, d_ent_src, d_ent_slot,
                         d_levelfronts, d_cbinv, d_csc_ptr, d_csc_row, d_csc_col, d_csc_pos_ent, d_csr_ptr,
                         d_csr_col, d_csr_pos, d_csr_pos_ent, d_mats, d_mats_f, d_rhs_vec, d_Q,
-                        d_diag_csc, d_diag_ent, d_ent_row, d_ent_col, d_mats_diag};
+                        d_diag_csc, d_diag_ent, d_ent_row, d_ent_col, d_mats_diag, d_flf};
         for (void* p : ptrs)
             if (p) cudaFree(p);
     }
@@ -313,6 +316,11 @@ struct Tuning {
     // 256-thread class: strip updates and Schur complement through the TMA-fed CTA-level GEMM
     // (default off: measured slower than the per-warp loops, profiles/r2_summary.md)
     int tma = 0;
+    // fronts whose pivot panels ((2 s - k) k elements) fit this many KB of shared memory go to
+    // factor_panel_kernel (0: class off); CTA width 64 up to order panel_nt64, 128 up to panel_nt128
+    // (measured at cfg1, factor phase: off 50.6 ms, 48 KB 50.3, 72 KB 52.1, 110 KB 54.0; DRAM traffic of
+    // the classes it replaces 45 -> 40 GB: these fronts are bound by their pivot chain, not by memory)
+    int panel_max = 48, panel_nt64 = 48, panel_nt128 = 96;
     Tuning() {
         auto geti = [](const char* name, int def) {
             const char* v = getenv(name);
@@ -332,6 +340,9 @@ struct Tuning {
         smem_nt64 = geti("JPB_SMEM_NT64", smem_nt64);
         smem_nt128 = geti("JPB_SMEM_NT128", smem_nt128);
         tma = geti("JPB_TMA", tma);
+        panel_max = std::min(200, geti("JPB_PANEL_MAX", panel_max));
+        panel_nt64 = geti("JPB_PANEL_NT64", panel_nt64);
+        panel_nt128 = geti("JPB_PANEL_NT128", panel_nt128);
     }
 };
 // symbolic options, overridable for tuning runs (JPB_LEAF, JPB_RELAX_SMALL, ...)
@@ -384,7 +395,7 @@ void factor(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* F, const cd
             int* status) {
     Span span(st, s, PH_FACTOR);
     for (int l = 0; l < P.S.nlevels; ++l) {
-        const int* lfl = P.d_levelfronts + P.levelptr[l];
+        const int* lfl = P.d_flf + P.flevelptr[l];
         for (const Pattern::FactorGroup& g : P.fgroups[l]) {
             const int64_t grid64 = (int64_t)g.count * nsys;
             if (grid64 > 0x7fffffff) throw InvalidArg("wave too large for one launch");
@@ -393,7 +404,11 @@ void factor(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* F, const cd
 #define JPB_FACTOR(KERNEL, NT)                                                                       \
     if (ent_order) KERNEL<true, NT><<<grid, NT, g.smem, s>>>(P.sd, lf, nsys, F, data, status);       \
     else KERNEL<false, NT><<<grid, NT, g.smem, s>>>(P.sd, lf, nsys, F, data, status);
-            if (g.smem) {
+            if (g.kind == 2) {
+                if (g.nt == 256) { JPB_FACTOR(factor_panel_kernel, 256) }
+                else if (g.nt == 128) { JPB_FACTOR(factor_panel_kernel, 128) }
+                else { JPB_FACTOR(factor_panel_kernel, 64) }
+            } else if (g.kind == 1) {
                 if (g.nt == 256) { JPB_FACTOR(factor_smem_kernel, 256) }
                 else if (g.nt == 128) { JPB_FACTOR(factor_smem_kernel, 128) }
                 else { JPB_FACTOR(factor_smem_kernel, 64) }
@@ -782,6 +797,11 @@ int jpb_create(jpb_state** out, int device) {
         auto setg = [&](auto kernel, int bytes) {
             ok &= cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) == cudaSuccess;
         };
+        for (int bytes : {204 * 1024}) {
+            setg(factor_panel_kernel<true, 256>, bytes); setg(factor_panel_kernel<false, 256>, bytes);
+            setg(factor_panel_kernel<true, 128>, bytes); setg(factor_panel_kernel<false, 128>, bytes);
+            setg(factor_panel_kernel<true, 64>, bytes); setg(factor_panel_kernel<false, 64>, bytes);
+        }
         setg(factor_level_kernel<true, 256, true>, GB_SMEM);
         setg(factor_level_kernel<false, 256, true>, GB_SMEM);
         setg(selftest_cta_gemm_kernel, GB_SMEM);
@@ -971,43 +991,60 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
         }
         P->wsolve[l] = {nabove, smax};
     }
-    // factor launch groups: fronts of a level are sorted largest first
+    // Factor launch groups.  Every level gets its own ordering of the fronts for the numeric
+    // phase (the solve kernels keep S.levelfronts, sorted by order): first the fronts handled in
+    // global memory (largest first, split by CTA width), then the fronts whose whole s x s block
+    // lives in shared memory (legacy class, JPB_PANEL_MAX=0), then the fronts whose PIVOT PANELS
+    // live in shared memory, bucketed by their shared-memory footprint.
     P->fgroups.assign(S.nlevels, {});
+    std::vector<int> flf;
+    flf.reserve(S.nfronts);
+    P->flevelptr.assign(S.nlevels + 1, 0);
     {
         const Tuning& tn = tuning();
-        auto group_of = [&](int sz, int& nt) {      // class id: 0..2 global, 3.. shared
-            if (sz > tn.smem_max) {
-                int c = sz > tn.front_big ? 0 : (sz > tn.front_mid ? 1 : 2);
-                nt = tn.nt[c];
-                return c;
-            }
-            nt = sz <= tn.smem_nt64 ? 64 : (sz <= tn.smem_nt128 ? 128 : 256);
-            return 3 + (sz + tn.smem_step - 1) / tn.smem_step;
-        };
+        struct Item { int f, kind, nt, smem; };
         for (int l = 0; l < S.nlevels; ++l) {
-            int prev = -1;
+            std::vector<Item> items;
             for (int q = S.levelptr[l]; q < S.levelptr[l + 1]; ++q) {
-                const int sz = S.f_s[S.levelfronts[q]];
-                int nt = 0;
-                const int c = group_of(sz, nt);
-                if (c != prev) {
-                    const int smem = c >= 3 ? sz * smem_ld(sz) * (int)sizeof(cd) : 0;
-                    P->fgroups[l].push_back({q - S.levelptr[l], 0, smem, nt});
-                    prev = c;
+                const int f = S.levelfronts[q], sz = S.f_s[f], kk = S.f_k[f];
+                const int64_t pbytes = (int64_t)panel_elems(sz, kk) * (int64_t)sizeof(cd);
+                Item it{f, 0, 0, 0};
+                if (tn.panel_max > 0 && pbytes <= (int64_t)tn.panel_max * 1024) {
+                    it.kind = 2;
+                    it.nt = sz <= tn.panel_nt64 ? 64 : (sz <= tn.panel_nt128 ? 128 : 256);
+                    it.smem = (int)(((pbytes + 4095) / 4096) * 4096);        // 4 KB buckets
+                } else if (sz <= tn.smem_max) {
+                    it.kind = 1;
+                    it.nt = sz <= tn.smem_nt64 ? 64 : (sz <= tn.smem_nt128 ? 128 : 256);
+                    const int top = ((sz + tn.smem_step - 1) / tn.smem_step) * tn.smem_step;   // group's largest order
+                    it.smem = (top * smem_ld(top) + TW * TW) * (int)sizeof(cd);
+                } else {
+                    const int c = sz > tn.front_big ? 0 : (sz > tn.front_mid ? 1 : 2);
+                    it.kind = 0;
+                    it.nt = tn.nt[c];
                 }
-                P->fgroups[l].back().count++;
+                items.push_back(it);
             }
-            // shared-memory-resident fronts keep a copy of the pivot tile behind the front for the
-            // Newton-Schulz polish of its inverse: (widest pivot tile of the group)^2 elements
-            for (Pattern::FactorGroup& g : P->fgroups[l]) {
-                if (!g.smem) continue;
-                int wk = 1;
-                for (int q = 0; q < g.count; ++q)
-                    wk = std::max(wk, std::min(TW, S.f_k[S.levelfronts[S.levelptr[l] + g.first + q]]));
-                g.smem += wk * wk * (int)sizeof(cd);
+            std::stable_sort(items.begin(), items.end(), [&](const Item& a, const Item& b) {
+                if (a.kind != b.kind) return a.kind < b.kind;
+                if (a.kind == 0) return false;                       // keep "largest first"
+                if (a.smem != b.smem) return a.smem > b.smem;
+                return a.nt > b.nt;
+            });
+            P->flevelptr[l] = (int)flf.size();
+            for (size_t q = 0; q < items.size(); ++q) {
+                const Item& it = items[q];
+                auto& groups = P->fgroups[l];
+                if (groups.empty() || groups.back().kind != it.kind || groups.back().nt != it.nt ||
+                    groups.back().smem != it.smem)
+                    groups.push_back({(int)q, 0, it.smem, it.nt, it.kind});
+                groups.back().count++;
+                flf.push_back(it.f);
             }
         }
+        P->flevelptr[S.nlevels] = (int)flf.size();
     }
+    P->d_flf = upload(flf);
     // inverse extend-add maps (parent contribution row -> child contribution row) and the
     // number of child rows that land on parent pivots; the factor kernel for large fronts
     // gathers the children's Schur blocks with them while it writes its own (no zero fill,

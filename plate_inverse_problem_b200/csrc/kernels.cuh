@@ -1236,6 +1236,193 @@ factor_smem_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd
     if (tid == 0 && ps.sing && status) atomicOr(status + b, 1);
 }
 
+// ------------------------------------------- pivot panels in shared memory (K2p)
+// Fronts whose PIVOT PANELS fit the SM's shared memory -- the k pivot rows (k x s: pivot block
+// and U12) and the pivot columns of the other rows (m x k: L21), (2 s - k) k elements instead of
+// the s^2 of factor_smem_kernel -- are factorised entirely out of shared memory: zero fill,
+// A entries, the pivot part of the children's contribution blocks, the pivot-tile inversion and
+// every DMMA operand (strips, Lt, Schur complement) hit the panels; the contribution block is
+// never resident: its 16 x 32 tiles are formed in registers from the panels, the children's
+// blocks are gathered into them through the inverse maps (as in factor_level_kernel) and each
+// element is written to HBM exactly once.  Compared with factor_smem_kernel a front of order 45
+// with 10 pivots needs 13 KB instead of 33 KB (2.6x the resident CTAs); compared with
+// factor_level_kernel a front of order 86 with 25 pivots reads its DMMA operands at ~30 cycles
+// instead of an L1/L2 round trip and never scatters into HBM.  HBM traffic = the compulsory
+// bytes: entries and child blocks in, panels and contribution block out.
+//
+// Layout: Up[k][ldu] (ldu = smem_ld(s)) followed by Lp[m][ldl] (ldl = smem_ld(k)); both leading
+// dimensions are 2 (mod 4), which keeps the DMMA B-fragment loads bank-conflict free.
+__host__ __device__ __forceinline__ int panel_elems(int s, int k) { return k * smem_ld(s) + (s - k) * smem_ld(k); }
+
+template <bool ENT_ORDER, int NT>
+__global__ void __launch_bounds__(NT, 512 / NT)
+factor_panel_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd* Fall,
+                    const cd* __restrict__ data, int* status) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ PivotSmem ps;
+    __shared__ ChildInfo chs[MAXCH];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = NT / 32;
+    const int b = blockIdx.x % nsys;
+    const FrontDesc fd = sd.fr[level_fronts[blockIdx.x / nsys]];
+    cd* Fsys = Fall + (int64_t)b * sd.front_slots;
+    cd* Fg = Fsys + fd.off;
+    const int s = fd.s, k = fd.k, ld = fd.ld, m = s - k;
+    const int ldu = smem_ld(s), ldl = smem_ld(k);
+    cd* Up = reinterpret_cast<cd*>(smem_raw);
+    cd* Lp = Up + k * ldu;
+
+    if (tid == 0) { ps.sing = 0; ps.swapped = 0; }
+    if (tid < fd.nchild && tid < MAXCH) {
+        const FrontDesc fc = sd.fr[sd.children[fd.childptr + tid]];
+        chs[tid].cb = fc.off + (int64_t)fc.k * fc.ld + fc.k;
+        chs[tid].ld = fc.ld;
+        chs[tid].invoff = fc.invoff;
+    }
+    {
+        const cd zero = make_double2(0.0, 0.0);
+        const int tot = k * ldu + m * ldl;
+        for (int e = tid; e < tot; e += NT) Up[e] = zero;
+    }
+    __syncthreads();
+    // A entries: every entry of the front has its row or its column among the pivots
+    {
+        const cd* db = data + (int64_t)b * sd.nnz;
+        const float inv_ld = 1.0f / (float)ld;
+        constexpr int MLP = 4;
+        for (int q0 = tid; q0 < fd.nent; q0 += MLP * NT) {
+            cd v[MLP];
+            int sl[MLP];
+#pragma unroll
+            for (int u = 0; u < MLP; ++u) {
+                const int q = q0 + u * NT;
+                if (q < fd.nent) {
+                    const int64_t gq = fd.entptr + q;
+                    sl[u] = __ldg(sd.ent_slot + gq);
+                    v[u] = ENT_ORDER ? db[gq] : db[__ldg(sd.ent_src + gq)];
+                } else {
+                    sl[u] = -1;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < MLP; ++u)
+                if (sl[u] >= 0) {
+                    const int i = __float2int_rz(((float)sl[u] + 0.5f) * inv_ld), j = sl[u] - i * ld;
+                    if (i < k) Up[i * ldu + j] = v[u];
+                    else Lp[(i - k) * ldl + j] = v[u];
+                }
+        }
+    }
+    __syncthreads();
+    // children: the part of their contribution blocks that lands on pivot rows or pivot columns
+    // (their first npan rows in full, then the first npan columns of the other rows)
+    for (int ci = 0; ci < fd.nchild; ++ci) {
+        const FrontDesc fc = sd.fr[sd.children[fd.childptr + ci]];
+        const int* rel = sd.relmap + fc.reloff;
+        const int mc = fc.s - fc.k, pc = fc.npan;
+        const cd* Fc = Fsys + fc.off + (int64_t)fc.k * fc.ld + fc.k;
+        const int top = pc * mc, tot = top + (mc - pc) * pc;
+        const float inv_mc = 1.0f / (float)mc, inv_pc = 1.0f / (float)max(pc, 1);
+        constexpr int MLP = 8;
+        for (int e0 = tid; e0 < tot; e0 += MLP * NT) {
+            cd v[MLP];
+            int dst[MLP];
+#pragma unroll
+            for (int q = 0; q < MLP; ++q) {
+                const int e = e0 + q * NT;
+                if (e < tot) {
+                    int i, j;
+                    if (e < top) { i = fast_div(e, mc, inv_mc); j = e - i * mc; }
+                    else { const int e2 = e - top; i = fast_div(e2, pc, inv_pc); j = e2 - i * pc; i += pc; }
+                    v[q] = Fc[(int64_t)i * fc.ld + j];
+                    const int pi = __ldg(rel + i), pj = __ldg(rel + j);
+                    dst[q] = pi < k ? pi * ldu + pj : k * ldu + (pi - k) * ldl + pj;      // offset from Up
+                } else {
+                    dst[q] = -1;
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < MLP; ++q)
+                if (dst[q] >= 0) {
+                    cd o = Up[dst[q]];
+                    o.x += v[q].x; o.y += v[q].y;
+                    Up[dst[q]] = o;
+                }
+        }
+        __syncthreads();
+    }
+
+    // left-looking block factorisation of the pivot tiles, operands in the panels
+    const int KT = (k + TW - 1) / TW;
+    const int nlp = (m + 15) >> 4;                      // 16-row tiles of the L panel
+    for (int J = 0; J < KT; ++J) {
+        const int j0 = J * TW;
+        const int jw = min(TW, k - j0);
+        const int j1 = j0 + jw;
+        if (J > 0) {
+            // (a) rows [j0, k) x cols [j0, j1) in Up, (b) rows [k, s) x cols [j0, j1) in Lp,
+            // (c) rows [j0, j1) x cols [j1, s) in Up; K = j0, B operand = Up[0:j0, cols]
+            const int na = (k - j0 + 15) >> 4;
+            const int nrr = (jw + 15) >> 4, nrc = (s - j1 + 31) >> 5;
+            const int ntiles = na + nlp + nrr * nrc;
+            for (int tile = warp; tile < ntiles; tile += NW) {
+                cd* Crow;
+                int ldc, c, mr, nc;
+                if (tile < na) {
+                    const int r = j0 + 16 * tile;
+                    Crow = Up + r * ldu; ldc = ldu; c = j0; mr = min(16, k - r); nc = jw;
+                } else if (tile < na + nlp) {
+                    const int r = 16 * (tile - na);
+                    Crow = Lp + r * ldl; ldc = ldl; c = j0; mr = min(16, m - r); nc = jw;
+                } else {
+                    const int q = tile - na - nlp;
+                    const int r = j0 + 16 * (q % nrr);
+                    c = j1 + 32 * (q / nrr);
+                    Crow = Up + r * ldu; ldc = ldu; mr = min(16, j1 - r); nc = min(32, s - c);
+                }
+                Acc<2, 4> acc;
+                acc.zero();
+                warp_gemm_shared<2, 4>(acc, Crow, ldc, mr, Up + c, ldu, nc, j0, lane);
+                store_tile<2, 4, true>(acc, Crow + c, ldc, mr, nc, lane);
+            }
+            __syncthreads();
+        }
+        invert_tile_inplace<NT>(Up + j0 * ldu + j0, ldu, jw, tid, ps);
+        // Lt: rows (j1, k) of Up and all rows of Lp, columns [j0, j1)  <-  F[rows, j0:j1] * D^-1
+        const int nlu = (k - j1 + 15) >> 4;
+        for (int tile = warp; tile < nlu + nlp; tile += NW) {
+            cd* Arow;
+            int lda, mr;
+            if (tile < nlu) { const int r = j1 + 16 * tile; Arow = Up + r * ldu + j0; lda = ldu; mr = min(16, k - r); }
+            else { const int r = 16 * (tile - nlu); Arow = Lp + r * ldl + j0; lda = ldl; mr = min(16, m - r); }
+            Acc<2, 4> acc;
+            acc.zero();
+            warp_gemm_shared<2, 4>(acc, Arow, lda, mr, Up + j0 * ldu + j0, ldu, jw, jw, lane);
+            store_tile<2, 4, false>(acc, Arow, lda, mr, jw, lane);
+        }
+        __syncthreads();
+    }
+    // contribution block: C = sum over children (gathered) - L21 * U12, written once to HBM
+    if (m > 0) {
+        cd* C = Fg + (int64_t)k * ld + k;
+        const int ntr = (m + 15) >> 4, ntc = (m + 31) >> 5;
+        for (int tile = warp; tile < ntr * ntc; tile += NW) {
+            const int rc = 16 * (tile % ntr), cc = 32 * (tile / ntr);
+            const int mr = min(16, m - rc), nc = min(32, m - cc);
+            Acc<2, 4> acc;
+            acc.zero();
+            warp_gemm_shared<2, 4>(acc, Lp + rc * ldl, ldl, mr, Up + k + cc, ldu, nc, k, lane);
+            store_tile_cb_inplace<2, 4>(acc, C + (int64_t)rc * ld + cc, ld, mr, nc, rc, cc, sd, fd, chs, Fsys, lane);
+        }
+    }
+    // the panels leave in one pass: pivot rows in full, then the pivot columns of the other rows
+    for (int i0 = warp; i0 < k; i0 += NW)
+        for (int j = lane; j < s; j += 32) Fg[(int64_t)i0 * ld + j] = Up[i0 * ldu + j];
+    for (int i0 = warp; i0 < m; i0 += NW)
+        for (int j = lane; j < k; j += 32) Fg[(int64_t)(k + i0) * ld + j] = Lp[i0 * ldl + j];
+    if (tid == 0 && ps.sing && status) atomicOr(status + b, 1);
+}
+
 // ------------------------------------------------------------------------ triangular solves
 
 // transposing warp reductions (see K3w below for their use)

@@ -339,14 +339,18 @@ def _run_variant(env, streams=1):
 
 
 def test_kernel_variants_agree():
-    """Every front-size class has two kernels (shared-memory-resident vs global-memory fronts in
-    the factorisation, warp-per-system vs CTA-per-front in the triangular solves); the size
+    """Every front-size class has several kernels (pivot panels in shared memory, whole front in
+    shared memory, global-memory fronts with per-warp or TMA-fed CTA-level GEMMs in the
+    factorisation; warp-per-system vs CTA-per-front in the triangular solves); the size
     thresholds are read once per process, so each setting runs in its own interpreter.  All
     settings must agree on FRF, loss and gradient far inside the parity tolerances, and so must
     the multi-stream sub-wave schedule."""
     base = _run_variant({})
-    variants = [({"JPB_SMEM_MAX": "0"}, 1), ({"JPB_SMEM_MAX": "112"}, 1), ({"JPB_WSOLVE_MAX": "0"}, 1),
-                ({"JPB_WSOLVE_MAX": "320"}, 1), ({"JPB_SMEM_STEP": "16", "JPB_FRONT_BIG": "96"}, 1), ({}, 3)]
+    variants = [({"JPB_PANEL_MAX": "0"}, 1), ({"JPB_PANEL_MAX": "0", "JPB_SMEM_MAX": "0"}, 1),
+                ({"JPB_PANEL_MAX": "0", "JPB_SMEM_MAX": "112"}, 1), ({"JPB_PANEL_MAX": "200"}, 1),
+                ({"JPB_PANEL_MAX": "16", "JPB_PANEL_NT64": "0", "JPB_PANEL_NT128": "0"}, 1),
+                ({"JPB_WSOLVE_MAX": "0"}, 1), ({"JPB_WSOLVE_MAX": "320"}, 1),
+                ({"JPB_PANEL_MAX": "0", "JPB_SMEM_STEP": "16", "JPB_FRONT_BIG": "96"}, 1), ({"JPB_TMA": "1"}, 1), ({}, 3)]
     for env, streams in variants:
         r = _run_variant(env, streams)
         assert relerr(np.array(r["fr"]), np.array(base["fr"])) <= 1e-9, env
