@@ -225,6 +225,29 @@ int jpb_dmma_peak(jpb_state* st, double* tflops);
 /* self test of the dense-front kernels against scalar device loops; returns max rel err */
 int jpb_selftest(jpb_state* st, double* max_err);
 
+/* ---- allocation-free residual check ---------------------------------------------------
+ * No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * For nsys systems on the pattern `solver_num` (registered earlier with jpb_add_mat, which is
+ * where all allocation happens): r[b] = rhs[b] - op(A_b) x[b] and the normwise backward error
+ * omega[b] = ||r[b]||_2 / || |A_b||x[b]| + |rhs[b]| ||_2 (moduli as |re| + |im|), the acceptance
+ * test of the solves.  It is the residual kernel of the refinement step (spmv_kernel<NORMS>)
+ * with its per-system norm accumulators in a file-scope `static __device__` array of
+ * 3 * JPB_NOALLOC_MAX_SYSTEMS doubles (96 KB on every GPU that loads the library, until exit)
+ * instead of a grow-only workspace: the call makes no cudaMalloc / cudaFree / allocating
+ * library call.  All five arrays are DEVICE pointers on the state's device, complex128 as
+ * interleaved doubles: mat [nsys, nnz] in the caller's CSC value order, x / rhs / r [nsys, N],
+ * omega [nsys] (real).  transpose != 0: op(A) = A^T (plain transpose, as jpb_solve).
+ * stream: a cudaStream_t to launch on (the call then returns without synchronising) or NULL =
+ * the state's stream, synchronised before return.  nsys > JPB_NOALLOC_MAX_SYSTEMS is rejected
+ * with JPB_EINVAL (split the batch).  Every call on a device shares the one array, which
+ * keeps the previous call's contents (the call clears what it uses first): calls that overlap
+ * on the GPU (different streams, or graphs replayed concurrently) race on it -- serialise them. */
+#define JPB_NOALLOC_MAX_SYSTEMS 4096
+int jpb_residual_noalloc(jpb_state* st, int solver_num, int transpose, int64_t nsys,
+                         const double* mat, const double* x, const double* rhs, double* r,
+                         double* omega, void* stream);
+
 /* ---- host-only view of the symbolic analysis (no CUDA device needed) ------------------
  * Used by the CPU test-suite to replay the multifrontal schedule in numpy and by tools
  * that want the ordering / fill statistics.  sizes: [0]=nfronts, [1]=len(rowidx),

@@ -25,7 +25,7 @@ EXPORTED_SYMBOLS = (
     "jpb_add_mat", "jpb_symbolic_info", "jpb_get_ordering", "jpb_solve", "jpb_matvec",
     "jpb_assemble", "jpb_register_components", "jpb_eval_forward", "jpb_eval_loss_grad",
     "jpb_eval_loss_grad_dev", "jpb_eval_candidates", "jpb_eval_candidates_dev", "jpb_eval_jacobian",
-    "jpb_eval_jacobian_dev", "jpb_last_timings", "jpb_dmma_peak", "jpb_selftest",
+    "jpb_eval_jacobian_dev", "jpb_last_timings", "jpb_dmma_peak", "jpb_selftest", "jpb_residual_noalloc",
     "jpb_host_analyze", "jpb_host_sizes", "jpb_host_export", "jpb_host_free",
 )
 
@@ -73,6 +73,7 @@ def load_library() -> C.CDLL:
     lib.jpb_last_timings.argtypes = [vp, dp]
     lib.jpb_dmma_peak.argtypes = [vp, dp]
     lib.jpb_selftest.argtypes = [vp, dp]
+    lib.jpb_residual_noalloc.argtypes = [vp, i32, i32, i64, vp, vp, vp, vp, vp, vp]
     lib.jpb_host_analyze.argtypes = [i64, i64, dp, dp, i32, C.POINTER(vp), C.c_char_p, i32]
     lib.jpb_host_sizes.argtypes = [vp, dp, dp]
     lib.jpb_host_export.argtypes = [vp] + [dp] * 14

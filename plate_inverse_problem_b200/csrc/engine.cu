@@ -11,11 +11,14 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <vector>
 
 #include <nvtx3/nvToolsExt.h>
+
+#include <math_constants.h>
 
 #include "kernels.cuh"
 #include "symbolic.h"
@@ -1666,3 +1669,73 @@ int jpb_host_export(const jpb_host_symbolic* h, int32_t* perm, int32_t* f_s, int
 void jpb_host_free(jpb_host_symbolic* h) { delete h; }
 
 }  // extern "C"
+
+// ------------------------------------------------------------ allocation-free residual check
+// Scratch of jpb_residual_noalloc: the three squared norms spmv_kernel<true> accumulates per
+// system.  File-scope device memory (96 KB on every device that loads the library, held until
+// exit) so that the call itself never allocates.  The name below is the HOST-side stand-in of
+// the symbol; kernels get the device address obtained with cudaGetSymbolAddress.
+namespace {
+constexpr int NOALLOC_MAX_SYSTEMS = JPB_NOALLOC_MAX_SYSTEMS;
+static __device__ __align__(256) double g_noalloc_norms[3 * NOALLOC_MAX_SYSTEMS];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mutex;
+double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+// device address of the scratch array on `device` (which must be current); resolved once per device
+cudaError_t noalloc_scratch(int device, double** out) {
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+        double* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_norms);
+        if (e != cudaSuccess) return e;
+        g_noalloc_ptr[device] = p;
+    }
+    *out = g_noalloc_ptr[device];
+    return cudaSuccess;
+}
+
+// omega[v] = ||r_v|| / || |A||x_v| + |b_v| ||  from the squared norms (0 for an all-zero system)
+__global__ void noalloc_omega_kernel(int nsys, const double* __restrict__ norms, double* __restrict__ omega) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nsys) return;
+    const double r2 = norms[3 * v], t2 = norms[3 * v + 1];
+    omega[v] = t2 > 0.0 ? sqrt(r2 / t2) : (r2 > 0.0 ? CUDART_INF : 0.0);
+}
+}  // namespace
+
+extern "C" int jpb_residual_noalloc(jpb_state* st, int solver_num, int transpose, int64_t nsys,
+                                    const double* mat, const double* x, const double* b, double* r,
+                                    double* omega, void* stream) {
+    if (!st) return JPB_EINVAL;
+    if (solver_num < 0 || solver_num >= (int)st->pats.size())
+        return fail(st, JPB_EINVAL, "residual_noalloc: solver_num out of range (no such pattern registered)");
+    if (!mat || !x || !b || !r || !omega) return fail(st, JPB_EINVAL, "residual_noalloc: null array");
+    if (nsys <= 0 || nsys > NOALLOC_MAX_SYSTEMS)
+        return fail(st, JPB_EINVAL, "residual_noalloc: %lld systems in one call, the static scratch holds at most %d "
+                    "(JPB_NOALLOC_MAX_SYSTEMS); split the batch", (long long)nsys, NOALLOC_MAX_SYSTEMS);
+    const Pattern& P = *st->pats[solver_num];
+    cudaError_t e = cudaSetDevice(st->device);
+    double* norms = nullptr;
+    if (e == cudaSuccess) e = noalloc_scratch(st->device, &norms);
+    if (e != cudaSuccess) return fail(st, JPB_ECUDA, "residual_noalloc: %s", cudaGetErrorString(e));
+    cudaStream_t s = stream ? (cudaStream_t)stream : st->stream;
+    // the array keeps what the previous call left: the accumulators start at zero
+    e = cudaMemsetAsync(norms, 0, (size_t)nsys * 24, s);
+    if (e != cudaSuccess) return fail(st, JPB_ECUDA, "residual_noalloc: %s", cudaGetErrorString(e));
+    const bool trans = transpose != 0;
+    const int N = P.S.N;
+    dim3 grid((N + 127) / 128, (unsigned)nsys);
+    spmv_kernel<true><<<grid, 128, 0, s>>>(N, P.S.nnz, trans ? P.d_csc_ptr : P.d_csr_ptr,
+                                           trans ? P.d_csc_row : P.d_csr_col, trans ? nullptr : P.d_csr_pos,
+                                           (const cd*)mat, 1, (const cd*)x, 1, 0, (const cd*)b, 1, 0, (cd*)r,
+                                           (int)nsys, norms, nullptr);
+    noalloc_omega_kernel<<<(int)((nsys + 127) / 128), 128, 0, s>>>((int)nsys, norms, omega);
+    st->launches += 2;
+    e = cudaGetLastError();
+    if (e == cudaSuccess && !stream) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return fail(st, JPB_ECUDA, "residual_noalloc: %s", cudaGetErrorString(e));
+    return JPB_OK;
+}
