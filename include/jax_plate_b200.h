@@ -47,7 +47,11 @@ enum {
 };
 
 /* loss types of Problem.getLossFunction (Problem.py:948-975) */
-enum { JPB_LOSS_MSE = 0, JPB_LOSS_RMSE = 1, JPB_LOSS_MSE_AFC = 2, JPB_LOSS_MSE_LOG_AFC = 3 };
+enum { JPB_LOSS_MSE = 0, JPB_LOSS_RMSE = 1, JPB_LOSS_MSE_AFC = 2, JPB_LOSS_MSE_LOG_AFC = 3,
+       /* complex read-out of the mid-plane symmetric path (Problem.py:415: fr = c0 + c.u, one read-out row):
+        * |fr - ref|^2 and |(fr - ref) / ref|^2 (Problem.py:948-960) with a COMPLEX reference, ref = [B]
+        * interleaved (re, im) doubles; the `fr` output stays the amplitude |fr| */
+       JPB_LOSS_MSE_COMPLEX = 5, JPB_LOSS_RMSE_COMPLEX = 6 };
 
 /* ---- life cycle ------------------------------------------------------------------- */
 int jpb_create(jpb_state** out, int device);

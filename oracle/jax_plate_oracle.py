@@ -561,3 +561,106 @@ class OracleProblem:
             ct_s[i] = lam @ self.plate.rhs_vec
             grad += np.real(ct_coef[i] @ dc[i] + ct_s[i] * ds[i])
         return L, grad, dict(fr=fr, U=U, ct_coef=ct_coef, ct_s=ct_s, coef=coef, s=s)
+
+
+# ----------------------------------------------------------------------------------------
+# mid-plane symmetric (bending-only) path  (Problem.py:228-308 set-up, :391-417 body)
+# ----------------------------------------------------------------------------------------
+def isotropic_d(params, h):
+    """`Material.py:394-404`."""
+    E, G, beta = params
+    nu = E / (2.0 * G) - 1.0
+    D = E * h ** 3 / (12.0 * (1.0 - nu ** 2))
+    return np.array([D, nu * D, 0.0, D, 0.0, D * (1 - nu) / 2]) * (1 + 1j * beta)
+
+
+def make_d_transform(kind: str, h: float, angles=None):
+    """`get_D_transform` of the reference's materials (`Material.py:394-406, 485-504, 766-784`)."""
+    if kind == "isotropic":
+        return lambda p, omega=None: isotropic_d(p, h)
+    if kind == "orthotropic":
+        return lambda p, omega=None: orthotropic_abd(p, h)[2]
+    if kind == "sol":
+        return lambda p, omega=None: sol_abd(p, h, angles)[2]
+    raise ValueError(kind)
+
+
+class OracleSymmProblem:
+    """The symmetric branch as the reference composes it: on the free DOFs
+    `A = -w^2 MInertia + sum_k D_k Ks_k / 2e`, `b = -w^2 fInertia + sum_k D_k fKs_k / 2e`,
+    `fr = c0 + c . u` (complex), the four losses on it, and the gradient by the adjoint
+    (JAX convention, as `OracleProblem.loss_and_grad`): with u_bar = dL/dRe(fr) - i dL/dIm(fr) times c,
+    lambda = A^-T u_bar, dL/dD_k = lambda^T (fKs_k - Ks_k u) / 2e."""
+
+    def __init__(self, ff: dict, d_transform, rho: float, h: float):
+        self.e = e = h / 2.0
+        self.Ks = [sps.csc_matrix(K) / 2.0 / e for K in ff["Ks"]]                 # Problem.py:419
+        self.fKs = np.asarray(ff["fKs"], dtype=np.float64) / 2.0 / e               # :420
+        self.MInertia = (rho * (sps.csc_matrix(ff["M"]) + 1.0 / 3.0 * e ** 2 * sps.csc_matrix(ff["L"]))).tocsc()
+        self.fInertia = rho * (np.asarray(ff["fM"]) + 1.0 / 3.0 * e ** 2 * np.asarray(ff["fL"]))
+        self.c = np.asarray(ff["interpolation_vector"], dtype=np.float64)
+        self.c0 = float(ff["interpolation_value_from_bc"])
+        self.transform = d_transform
+        self.n = self.MInertia.shape[0]
+        self.exact = False
+
+    def system(self, f, params):
+        omega = 2.0 * np.pi * f
+        D = self.transform(np.asarray(params, dtype=np.float64), omega)
+        A = -(omega ** 2) * self.MInertia.astype(np.complex128)
+        b = -(omega ** 2) * self.fInertia.astype(np.complex128)
+        for k in range(6):
+            A = A + D[k] * self.Ks[k]
+            b = b + D[k] * self.fKs[k]
+        return sps.csc_matrix(A), b, D
+
+    def factor(self, A):
+        lu = umfpack_standin_lu(A)
+        return ExtendedLU(A, lu) if self.exact else lu
+
+    def forward(self, freqs, params, return_u=False):
+        freqs = np.atleast_1d(np.asarray(freqs, dtype=np.float64))
+        fr = np.zeros(freqs.size, dtype=np.complex128)
+        U = np.zeros((freqs.size, self.n), dtype=np.complex128)
+        for i, f in enumerate(freqs):
+            A, b, _ = self.system(f, params)
+            U[i] = self.factor(A).solve(b)
+            fr[i] = self.c0 + self.c @ U[i]
+        return (fr, U) if return_u else fr
+
+    def d_jacobian(self, params, rel_step=1e-3):
+        """d D_k / d p_j by the 4th-order central difference of `coefficient_jacobian`."""
+        params = np.asarray(params, dtype=np.float64)
+        dD = np.zeros((6, params.size), dtype=np.complex128)
+        for j in range(params.size):
+            hstep = rel_step * max(abs(params[j]), 1e-300)
+            for k, w in ((-2, 1 / 12), (-1, -8 / 12), (1, 8 / 12), (2, -1 / 12)):
+                p = params.copy()
+                p[j] += k * hstep
+                dD[:, j] += w * self.transform(p, None) / hstep
+        return dD
+
+    def loss_and_grad(self, freqs, params, ref, func_type):
+        freqs = np.atleast_1d(np.asarray(freqs, dtype=np.float64))
+        ref = np.asarray(ref)
+        F = freqs.size
+        dD = self.d_jacobian(params)
+        grad = np.zeros(len(params))
+        fr = np.zeros(F, dtype=np.complex128)
+        for i, f in enumerate(freqs):
+            A, b, D = self.system(f, params)
+            lu = self.factor(A)
+            u = lu.solve(b)
+            fr[i] = self.c0 + self.c @ u
+            if func_type == "MSE":
+                ybar = 2 * np.conj(fr[i] - ref[i]) / F
+            elif func_type == "RMSE":
+                ybar = 2 * np.conj(fr[i] - ref[i]) / abs(ref[i]) ** 2 / F
+            else:
+                a, ar = abs(fr[i]), abs(ref[i])
+                dfr = loss_dfr(np.array([a]), np.array([ar]), func_type)[0] * 1 / F
+                ybar = dfr * np.conj(fr[i]) / a
+            lam = lu.solve(ybar * self.c.astype(np.complex128), trans="T")
+            ctD = np.array([lam @ (self.fKs[k] - self.Ks[k] @ u) for k in range(6)])
+            grad += np.real(ctD @ dD)
+        return loss_value(fr, ref, func_type), grad, dict(fr=fr)

@@ -82,10 +82,20 @@ def union_pattern_and_align(mats, N: int):
 
 
 class Problem:
+    def __new__(cls, geometry=None, material=None, accelerometer=None, *args, **kw):
+        # `Problem.py:228`: a mid-plane symmetric material without an accelerometer takes the
+        # bending-only path (ProblemSymm.SymmetricProblem), everything else the unsymmetric one
+        if cls is Problem and accelerometer is None and material is not None and material.is_mps:
+            from .ProblemSymm import SymmetricProblem
+            return object.__new__(SymmetricProblem)
+        return object.__new__(cls)
+
     def __init__(self, geometry: Geometry, material: Material, accelerometer: AccelerometerParams,
                  ref_fr=None, *, cpu: int = 0, device: int = None, refinement: int = None,
                  refinement_threshold=None):
-        import os
+        if accelerometer is None:
+            raise ValueError("the unsymmetric path needs an accelerometer (Problem.py:228, 310); without one the "
+                             "material must be mid-plane symmetric")
         self.geometry, self.material, self.accelerometer = geometry, material, accelerometer
         self.reference_fr = ref_fr
         self.n_cpu = cpu    # accepted for interface parity; the batch loop runs on the GPU
@@ -94,11 +104,7 @@ class Problem:
         ff = geometry.matrices
         ff = ff.as_tuple() if hasattr(ff, "as_tuple") else ff
         mats = list(ff[0])
-        self.mat_size = N = mats[0].shape[0]
-        nz_idx, (mat, mat_T, coo_indices, perm), self.mats = union_pattern_and_align(mats, N)
-        self.sparsity = nz_idx.shape[0] / N ** 2
-        self.nz_mask = (coo_indices[:, 0], coo_indices[:, 1])
-        self.vec = np.ascontiguousarray(ff[1], dtype=np.float64)
+        N = mats[0].shape[0]
         self.interp_mat, self.interp_mat_Lh = np.asarray(ff[2]), np.asarray(ff[3])
         self.Lh_size, self.Mh_size, self.mesh = ff[4], ff[5], ff[6]
         self.interp_mat_Wx, self.interp_mat_Wy = np.asarray(ff[7]), np.asarray(ff[8])
@@ -119,10 +125,21 @@ class Problem:
         Q[1, Lh:2 * Lh] = mL
         Q[1, 2 * Lh:] = -hh * self.interp_mat_Wy.mean(axis=0)
         Q[2, 2 * Lh:] = self.interp_mat.mean(axis=0)
-        self.Q = Q
         ts = acc.transverse_sensitivity
-        self.weights = np.array([ts ** 2, ts ** 2, 1.0])
-        # native state
+        self._setup_native(mats, ff[1], Q, np.array([ts ** 2, ts ** 2, 1.0]), device=device,
+                           refinement=refinement, refinement_threshold=refinement_threshold)
+
+    def _setup_native(self, mats, rhs_vec, Q, weights, *, device=None, refinement=None, refinement_threshold=None):
+        """Pattern union + alignment (`Problem.py:317-345`), registration of the pattern, the
+        component matrices, the right-hand-side vector and the read-out rows with the CUDA library."""
+        import os
+        self.mat_size = N = mats[0].shape[0]
+        nz_idx, (mat, mat_T, coo_indices, perm), self.mats = union_pattern_and_align(mats, N)
+        self.sparsity = nz_idx.shape[0] / N ** 2
+        self.nz_mask = (coo_indices[:, 0], coo_indices[:, 1])
+        self.vec = np.ascontiguousarray(rhs_vec, dtype=np.float64)
+        self.Q = Q = np.ascontiguousarray(Q, dtype=np.float64)
+        self.weights = np.ascontiguousarray(weights, dtype=np.float64)
         if device is None:
             device = int(os.environ.get("LOCAL_RANK", "0"))
         self._st = st = _lib.State(device)
@@ -146,8 +163,8 @@ class Problem:
             refinement_threshold is None or float(np.atleast_1d(refinement_threshold)[0]) > 0)
         self.mats = np.ascontiguousarray(self.mats)
         st.check(st.lib.jpb_register_components(st.h, self.solver_num, self.mats.shape[0],
-                                                _lib.ptr(self.mats), _lib.ptr(self.vec), 3,
-                                                _lib.ptr(np.ascontiguousarray(Q))))
+                                                _lib.ptr(self.mats), _lib.ptr(self.vec), Q.shape[0],
+                                                _lib.ptr(Q)))
 
     # ---- helpers -------------------------------------------------------------------------
     @property
@@ -169,7 +186,7 @@ class Problem:
         coef, s, _, _ = self.coefficients(freqs, params)
         F = freqs.size
         coef, s = np.ascontiguousarray(coef), np.ascontiguousarray(s)
-        y = np.zeros((F, 3), dtype=np.complex128)
+        y = np.zeros((F, self.Q.shape[0]), dtype=np.complex128)
         u = np.zeros((F, self.mat_size), dtype=np.complex128) if return_u else None
         st = self._st
         st.check(st.lib.jpb_eval_forward(st.h, self.solver_num, F, _lib.ptr(coef), _lib.ptr(s),
@@ -196,25 +213,26 @@ class Problem:
         """`Problem.py:933-980`.  Returns `loss(params) -> float` with the extra method
         `loss.value_and_grad(params) -> (float, grad[P])`."""
         frequencies = np.atleast_1d(np.asarray(frequencies, dtype=np.float64))
-        reference_fr = _real_reference(reference_fr)
-        assert frequencies.shape[0] == reference_fr.shape[0]
         if func_type not in _lib.LOSS_TYPES:
             raise ValueError(f'Function type "{func_type}" is not supported!')
+        assert frequencies.shape[0] == np.asarray(reference_fr).shape[0]
+        reference_in = reference_fr
+        # the reference as the device takes it: `unit` doubles per frequency
+        reference_fr, ltype, unit = self._loss_reference(reference_fr, func_type)
         scaling = 1.0 if scaling_params is None else np.array(scaling_params, dtype=np.float64)
         F = frequencies.size
-        ltype = _lib.LOSS_TYPES[func_type]
 
         def value_and_grad(params):
             p = np.asarray(params, dtype=np.float64) * scaling
             if p.ndim == 2:
-                L, g = self._candidates_value_and_grad(frequencies, reference_fr, ltype, p)
+                L, g = self._candidates_value_and_grad(frequencies, reference_fr, ltype, p, unit)
                 return L, g * scaling
 
             def local(lo, hi):
                 nloc = hi - lo
                 coef, s, _, _ = self.coefficients(frequencies[lo:hi], p, with_jacobian=False)
                 coef, s = np.ascontiguousarray(coef), np.ascontiguousarray(s)
-                ref = np.ascontiguousarray(reference_fr[lo:hi])
+                ref = np.ascontiguousarray(reference_fr[unit * lo:unit * hi])
                 fr, loss_sum = np.zeros(nloc), np.zeros(1)
                 ct = np.zeros((nloc, coef.shape[1]), dtype=np.complex128)
                 cts = np.zeros(nloc, dtype=np.complex128)
@@ -240,17 +258,24 @@ class Problem:
 
         def loss(params):
             fr = fr_function(frequencies, np.asarray(params, dtype=np.float64) * scaling)
-            return float(np.mean(_residuals(fr, reference_fr, func_type)[0] ** 2))
+            return self._loss_value(fr, reference_in, func_type)
 
         loss.value_and_grad = value_and_grad
         loss.grad = lambda params: value_and_grad(params)[1]
         # the Gauss-Newton model of the same loss, for Optimizers.optimize_lm / method="gn"
-        loss.gauss_newton = self.getGaussNewtonModel(frequencies, reference_fr, func_type, scaling_params)
+        loss.gauss_newton = self.getGaussNewtonModel(frequencies, reference_in, func_type, scaling_params)
         loss.__name__ = func_type + "Loss"
         return loss
 
+    def _loss_reference(self, reference_fr, func_type):
+        """(reference as the device takes it, C-ABI loss type, doubles per frequency)."""
+        return _real_reference(reference_fr), _lib.LOSS_TYPES[func_type], 1
+
+    def _loss_value(self, fr, reference_fr, func_type):
+        return float(np.mean(_residuals(fr, _real_reference(reference_fr), func_type)[0] ** 2))
+
     # ---- batched parameter candidates (BASELINE configs[4]) --------------------------------
-    def _candidates_value_and_grad(self, frequencies, reference_fr, ltype, cands):
+    def _candidates_value_and_grad(self, frequencies, reference_fr, ltype, cands, unit=1):
         """C candidates x F frequencies as ONE flattened batch of C*F systems, sharded
         contiguously over the ranks; per-candidate loss sums are segmented on the device
         (`jpb_eval_candidates`), the only exchange is one all-reduce of [C, 1+P]."""
@@ -270,7 +295,7 @@ class Problem:
             dc, ds = np.concatenate(dcs)[sl], np.concatenate(dss)[sl]
             n = hi - lo
             cand = np.ascontiguousarray((np.arange(lo, hi) // F).astype(np.int32))
-            ref = np.ascontiguousarray(np.tile(reference_fr, c1 - c0)[sl])
+            ref = np.ascontiguousarray(np.tile(reference_fr, c1 - c0)[unit * sl.start:unit * sl.stop])
             fr, loss_sum = np.zeros(n), np.zeros(C_)
             ct = np.zeros((n, coef.shape[1]), dtype=np.complex128)
             cts = np.zeros(n, dtype=np.complex128)

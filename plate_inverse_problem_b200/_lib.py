@@ -17,6 +17,7 @@ LIB_PATH = os.environ.get("JPB_LIB_PATH") or os.path.join(_HERE, "libjaxplate_b2
 
 JPB_OK, JPB_EINVAL, JPB_ECUDA, JPB_ESINGULAR, JPB_ENOMEM, JPB_ESTATE = range(6)
 LOSS_TYPES = {"MSE": 0, "RMSE": 1, "MSE_AFC": 2, "MSE_LOG_AFC": 3}
+COMPLEX_LOSS_TYPES = {"MSE": 5, "RMSE": 6, "MSE_AFC": 2, "MSE_LOG_AFC": 3}
 
 # every symbol include/jax_plate_b200.h declares
 EXPORTED_SYMBOLS = (

@@ -692,7 +692,8 @@ void eval_core(jpb_state* st, cudaStream_t s, Pattern& P, int64_t B, const cd* c
         if (!adjoint) return;
         {
             Span span(st, sc, PH_READOUT);
-            loss_kernel<<<(n + 127) / 128, 128, 0, sc>>>(n, R, y + g0 * R, w, ref ? ref + g0 : nullptr,
+            loss_kernel<<<(n + 127) / 128, 128, 0, sc>>>(n, R, y + g0 * R, w,
+                                                         ref ? ref + (loss_type >= 5 ? 2 : 1) * g0 : nullptr,
                                                          loss_type, 1.0 / (double)F_total, fr + g0,
                                                          loss_term + g0, ybar + l0 * R);
             launch_check(st);
@@ -1383,7 +1384,9 @@ void check_eval_args(Pattern& P, int64_t B, const void* coef, const void* rhs_sc
                      const void* ct_coef, const void* ct_s, const int* seg, int nseg) {
     if (!coef || !rhs_scale || !w || !fr || !ct_coef || !ct_s || B <= 0)
         throw InvalidArg("eval_loss_grad: bad arguments");
-    if (loss_type < 0 || loss_type > 4) throw InvalidArg("eval_loss_grad: unknown loss type");
+    if (loss_type < 0 || loss_type > 6) throw InvalidArg("eval_loss_grad: unknown loss type");
+    if (loss_type >= 5 && P.R != 1)
+        throw InvalidArg("eval_loss_grad: the complex losses (types 5, 6) need a single read-out row");
     if (loss_type != 4 && (!ref || !loss_sum || F_total < 1)) throw InvalidArg("eval_loss_grad: bad arguments");
     if (nseg < 1 || (nseg > 1 && !seg)) throw InvalidArg("eval_loss_grad: bad candidate segments");
     if (B > INT32_MAX) throw InvalidArg("eval_loss_grad: batch too large");
@@ -1406,10 +1409,11 @@ int eval_host(jpb_state* st, int solver_num, int64_t B, const double* coef, cons
     cudaStream_t s = st->stream;
     const int K = P.K, R = P.R;
     // device staging block, inputs first and results last so that each direction is one copy:
-    //   in : coef [B,K] c, scale [B] c, ref [B] d, w [4] d, seg [B] i
+    //   in : coef [B,K] c, scale [B] c, ref [B] d (c for the complex losses), w [4] d, seg [B] i
     //   -- : y [B,R] c (device only)
     //   out: ct_coef [B,K] c, ct_s [B] c, fr [B] d, loss [nseg] d, status [B] i
-    const size_t in_bytes = ((size_t)B * (K * 16 + 16 + 8 + 4) + 32 + 15) & ~(size_t)15;
+    const size_t in_bytes = ((size_t)B * (K * 16 + 16 + 16 + 4) + 32 + 15) & ~(size_t)15;
+    const int ref_doubles = loss_type >= 5 ? 2 : 1;
     const size_t y_bytes = (size_t)B * R * 16;
     const size_t out_bytes = (size_t)B * (K * 16 + 16 + 8 + 4) + (size_t)nseg * 8 + 16;
     char* stage = (char*)st->hstage.get(in_bytes + y_bytes + out_bytes + 64);
@@ -1417,7 +1421,7 @@ int eval_host(jpb_state* st, int solver_num, int64_t B, const double* coef, cons
     cd* dcoef = (cd*)stage;
     cd* dscale = dcoef + B * K;
     double* dref = (double*)(dscale + B);
-    double* dw = dref + B;
+    double* dw = dref + 2 * B;
     int* dseg = (int*)(dw + 4);
     cd* dy = (cd*)(stage + in_bytes);
     char* dout = stage + in_bytes + y_bytes;
@@ -1430,7 +1434,7 @@ int eval_host(jpb_state* st, int solver_num, int64_t B, const double* coef, cons
         Span span(st, s, PH_H2D);
         memcpy(pin, coef, (size_t)B * K * 16);
         memcpy(pin + ((char*)dscale - stage), rhs_scale, (size_t)B * 16);
-        if (ref) memcpy(pin + ((char*)dref - stage), ref, (size_t)B * 8);
+        if (ref) memcpy(pin + ((char*)dref - stage), ref, (size_t)B * 8 * ref_doubles);
         memcpy(pin + ((char*)dw - stage), w, (size_t)R * 8);
         if (seg) memcpy(pin + ((char*)dseg - stage), seg, (size_t)B * 4);
         CK(cudaMemcpyAsync(stage, pin, in_bytes, cudaMemcpyHostToDevice, s));

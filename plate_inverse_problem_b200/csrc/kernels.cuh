@@ -2179,7 +2179,7 @@ __global__ void loss_kernel(int B, int R, const cd* __restrict__ y, const double
         cd v = y[(int64_t)b * R + r];
         s2 += w[r] * (v.x * v.x + v.y * v.y);
     }
-    const double f = sqrt(s2), rf = ref ? ref[b] : 1.0;
+    const double f = sqrt(s2), rf = (ref && loss_type < 5) ? ref[b] : 1.0;
     double term, dfr;
     if (loss_type == 4) {            // identity: the cotangent of fr itself (Jacobian rows)
         term = f; dfr = 1.0; inv_F = 1.0;
@@ -2189,8 +2189,21 @@ __global__ void loss_kernel(int B, int R, const cd* __restrict__ y, const double
         double q = (f - rf) / rf; term = q * q; dfr = 2.0 * (f - rf) / (rf * rf);
     } else if (loss_type == 2) {     // MSE_AFC
         double q = fabs(f) - fabs(rf); term = q * q; dfr = 2.0 * q * (f >= 0.0 ? 1.0 : -1.0);
-    } else {                         // MSE_LOG_AFC
+    } else if (loss_type == 3) {     // MSE_LOG_AFC
         double q = log(fabs(f)) - log(fabs(rf)); term = q * q; dfr = 2.0 * q / f;
+    } else {
+        // complex read-out (R = 1, mid-plane symmetric path, Problem.py:415 with the losses of :948-960):
+        // 5: |y - ref|^2, 6: |(y - ref) / ref|^2 with a COMPLEX reference (ref = [B] interleaved
+        // re, im); cotangent ybar = 2 conj(y - ref) [/ |ref|^2]
+        const cd rc = reinterpret_cast<const cd*>(ref)[b];
+        const cd v = y[b];
+        const double dx = v.x - rc.x, dy = v.y - rc.y;
+        const double sc = loss_type == 6 ? 1.0 / (rc.x * rc.x + rc.y * rc.y) : 1.0;
+        fr[b] = f;
+        loss_term[b] = (dx * dx + dy * dy) * sc;
+        const double c = 2.0 * sc * inv_F;
+        ybar[b] = make_double2(c * dx, -c * dy);
+        return;
     }
     fr[b] = f;
     loss_term[b] = term;

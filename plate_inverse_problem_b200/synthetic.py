@@ -514,3 +514,102 @@ def load_plate(path) -> SyntheticPlate:
                      float(z["mesh_extent"][1]))
     return SyntheticPlate(mats, z["rhs_vec"], z["interp_mat"], z["interp_mat_Lh"], int(z["Lh"]), int(z["Mh"]),
                           mesh, z["interp_mat_Wx"], z["interp_mat_Wy"], tuple(z["test_point"]))
+
+
+# ------------------------------------------------------------------------------------------
+# Mid-plane symmetric (bending-only) plates: the output of `load_matrices_symm`
+# (`pyFFInterface.py:10-167`) without FreeFem++.  One Morley field w; the clamped DOFs are
+# ELIMINATED (the reference keeps the free rows / columns and moves the boundary values to the
+# right-hand side, `evaluateMatrixAndRHS` `:81-117`).  The reference densifies every matrix
+# (`.todense()`, `:99`); here they stay sparse (CSR) -- `dense=True` gives the reference's arrays.
+
+SYMM_MODULI = ("11", "12", "16", "22", "26", "66")      # MODULI_INDICES of the reference
+
+
+def bending_plate_from_mesh(mesh: PlateMesh, test_point, r_accel: float = 3.8e-3, dense: bool = False) -> dict:
+    """Keys as returned by `load_matrices_symm` (`pyFFInterface.py:149-166`): `Ks` [6] and `M`,
+    `L`, `MCorrection`, `LCorrection` on the free DOFs, their boundary vectors `fKs` [6, n],
+    `fM`, `fL`, ..., `interpolation_vector` [n], `interpolation_value_from_bc`,
+    `test_point_coord`, `constrained_idx` (bool over all DOFs), `mesh`, `boundary_value`."""
+    nv, ne = mesh.points.shape[0], mesh.edges.shape[0]
+    Mh = nv + ne
+    area, _, _ = _p1_gradients(mesh)
+    xtest, ytest = test_point
+    cent = mesh.points[mesh.tris].mean(axis=1)
+    ind = ((cent[:, 0] - xtest) ** 2 + (cent[:, 1] - ytest) ** 2 <= r_accel ** 2 + 1e-8).astype(np.float64)
+    a = area[:, None, None]
+    C, xc, hs = _morley_coefficients(mesh)
+    mdof = np.concatenate([mesh.tris, nv + mesh.tri_edges], axis=1)
+    wxx = 2.0 * C[:, 3, :] / hs[:, None] ** 2
+    wxy = C[:, 4, :] / hs[:, None] ** 2
+    wyy = 2.0 * C[:, 5, :] / hs[:, None] ** 2
+    Rm = np.repeat(mdof[:, :, None], 6, axis=2)
+    Cm = np.repeat(mdof[:, None, :], 6, axis=1)
+
+    def form(dv, du):                                  # area * d2(v)_i * d2(u)_j, rows = test function v
+        return _scatter(Mh, Mh, Rm, Cm, a * dv[:, :, None] * du[:, None, :])
+
+    # varf K11 .. K66 of pyFFInterface.py:50-55
+    total = {
+        "K11": form(wxx, wxx),
+        "K12": form(wxx, wyy) + form(wyy, wxx),
+        "K16": 2.0 * (form(wxx, wxy) + form(wxy, wxx)),
+        "K22": form(wyy, wyy),
+        "K26": 2.0 * (form(wyy, wxy) + form(wxy, wyy)),
+        "K66": 4.0 * form(wxy, wxy),
+    }
+    pts = mesh.points[mesh.tris]
+    qp = np.einsum("qk,tkd->tqd", _QUAD_BARY, pts)
+    qs = (qp - xc[:, None, :]) / hs[:, None, None]
+    x, y = qs[..., 0], qs[..., 1]
+    one, zero = np.ones_like(x), np.zeros_like(x)
+    mono = np.stack([one, x, y, x * x, x * y, y * y], axis=-1)
+    mdx = np.stack([zero, one, zero, 2 * x, y, zero], axis=-1) / hs[:, None, None]
+    mdy = np.stack([zero, zero, one, zero, x, 2 * y], axis=-1) / hs[:, None, None]
+    val, vdx, vdy = mono @ C, mdx @ C, mdy @ C
+    wq = _QUAD_W[None, :] * area[:, None]
+    m = np.einsum("tq,tqi,tqj->tij", wq, val, val)
+    l = np.einsum("tq,tqi,tqj->tij", wq, vdx, vdx) + np.einsum("tq,tqi,tqj->tij", wq, vdy, vdy)
+    total["M"] = _scatter(Mh, Mh, Rm, Cm, m)
+    total["L"] = _scatter(Mh, Mh, Rm, Cm, l)
+    total["MCorrection"] = _scatter(Mh, Mh, Rm, Cm, m * ind[:, None, None])
+    total["LCorrection"] = _scatter(Mh, Mh, Rm, Cm, l * ind[:, None, None])
+
+    # boundary values: funcBC = 1 on the clamped vertex values, 0 on the clamped normal derivatives
+    constrained = np.concatenate([mesh.clamped_vertices, mesh.clamped_edges]).astype(bool)
+    free = ~constrained
+    f_bc = np.zeros(Mh)
+    f_bc[:nv][mesh.clamped_vertices] = 1.0
+
+    def reduce(Kt):                                    # evaluateMatrixAndRHS, :81-117
+        Kt = Kt.tocsr()
+        K = Kt[free][:, free].tocsr()
+        rhs = -np.asarray(Kt[constrained][:, free].T @ f_bc[constrained]).ravel()
+        return (np.asarray(K.todense()) if dense else K), rhs
+
+    out = {}
+    for name in ("M", "L", "MCorrection", "LCorrection"):
+        out[name], out["f" + name] = reduce(total[name])
+    Ks, fKs = zip(*[reduce(total["K" + ss]) for ss in SYMM_MODULI])
+    out["Ks"] = np.array(Ks) if dense else list(Ks)
+    out["fKs"] = np.array(fKs)
+    # value of w at the test point (row 0 of `interpC`, :35-36)
+    tri, _ = _locate(mesh, np.array([[xtest, ytest]]))
+    s = (np.array([xtest, ytest]) - xc[tri[0]]) / hs[tri[0]]
+    mono_t = np.array([1.0, s[0], s[1], s[0] * s[0], s[0] * s[1], s[1] * s[1]])
+    iv = np.zeros(Mh)
+    np.add.at(iv, mdof[tri[0]], mono_t @ C[tri[0]])
+    out["interpolation_value_from_bc"] = float(iv[constrained] @ f_bc[constrained])
+    out["interpolation_vector"] = iv[free]
+    out["test_point_coord"] = np.array([xtest, ytest])
+    out["constrained_idx"] = constrained
+    out["mesh"] = mesh
+    out["boundary_value"] = f_bc
+    return out
+
+
+def make_bending_plate(nx: int, ny: int, Lx: float = 99.9e-3, Ly: float = 20e-3, r_accel: float = 3.8e-3,
+                       keep=None, dense: bool = False) -> dict:
+    """`load_matrices_symm` output for the cantilever strip of `make_plate` (same meshes)."""
+    mesh = rectangle_mesh(nx, ny, Lx, Ly) if keep is None else shaped_plate_mesh(nx, ny, Lx, Ly, keep)
+    return bending_plate_from_mesh(mesh, (r_accel, Ly / 2 - r_accel), r_accel, dense)

@@ -298,6 +298,43 @@ def optimizer_fixture(pkg):
     return out
 
 
+SYMM_CASES = {      # name -> (nx, ny, material kind, constructor args after density, perturbation of the parameters)
+    "iso_tiny": (6, 2, "Isotropic", (200e9, 77e9, 0.003), (1.1, 1.05, 2.0)),
+    "ortho_small": (30, 4, "Orthotropic", (130e9, 9e9, 5e9, 0.3, 0.01), (1.1, 1.1, 1.2, 1.0, 1.5)),
+}
+
+
+def symm_fixture(pkg):
+    """The mid-plane symmetric branch of the reference (complex FRF, four losses, FD gradient of the
+    reference's own loss) on bending-only synthetic plates; see ref_shim.reference_symm_problem."""
+    from plate_inverse_problem_b200.synthetic import make_bending_plate
+    out = {}
+    for name, (nx, ny, kind, args, pert) in SYMM_CASES.items():
+        rho = 7800.0 if kind == "Isotropic" else RHO
+        mat = getattr(pkg.Material, kind)(rho, *args)
+        prob = ref_shim.reference_symm_problem(pkg, make_bending_plate(nx, ny, dense=True), mat, H)
+        p0 = np.asarray(mat.get_parameters(), dtype=np.float64)
+        freqs = np.sort(np.concatenate([np.linspace(40.0, 600.0, 6), [83.0]]))
+        fr = np.asarray(prob.solveForward(freqs))
+        ref = np.asarray(prob.solveForward(freqs, p0 * np.array(pert)))
+        out[f"{name}_rho"], out[f"{name}_params"], out[f"{name}_freqs"] = np.array(rho), p0, freqs
+        out[f"{name}_fr"], out[f"{name}_ref"] = fr, ref
+        out[f"{name}_nnz"] = np.array(prob.M.shape[0])
+        out[f"{name}_D"] = np.asarray(mat.get_D_transform(H)(p0, 2 * np.pi * 100.0))
+        for lt in ("MSE", "RMSE", "MSE_AFC", "MSE_LOG_AFC"):
+            lf = prob.getLossFunction(freqs, ref, lt)
+            out[f"{name}_loss_{lt}"] = np.array(float(lf(p0)))
+            g = np.zeros(p0.size)
+            for j in range(p0.size):
+                h = 1e-4 * p0[j]
+                for k, w in ((-2, 1 / 12), (-1, -8 / 12), (1, 8 / 12), (2, -1 / 12)):
+                    p = p0.copy()
+                    p[j] += k * h
+                    g[j] += w * float(lf(p)) / h
+            out[f"{name}_fd_grad_{lt}"] = g
+    return out
+
+
 def check(pkg):
     """--check: recompute the quick parts and compare with the committed fixtures."""
     bad = []
@@ -318,6 +355,7 @@ def check(pkg):
     tiny, prob, rec = problem_fixture(pkg, "tiny", 9, full=False)
     tiny.update(rules_fixture(pkg, prob, rec))
     cmp("tiny", tiny, np.load(os.path.join(OUT, "ref_tiny.npz")), 1e-11)
+    cmp("symm", symm_fixture(pkg), np.load(os.path.join(OUT, "ref_symm.npz")), 1e-9)
     if bad:
         print("MISMATCH", bad)
         sys.exit(1)
@@ -328,6 +366,10 @@ def main():
     pkg = ref_shim.load("compiled")
     if "--check" in sys.argv:
         return check(pkg)
+    if "--only-input" not in sys.argv:
+        np.savez_compressed(os.path.join(OUT, "ref_symm.npz"), **symm_fixture(pkg))
+    if "--only-symm" in sys.argv:
+        return
     np.savez_compressed(os.path.join(OUT, "ref_input.npz"), **input_fixture(pkg))
     np.savez_compressed(os.path.join(OUT, "ref_optim.npz"), **optimizer_fixture(pkg))
     if "--only-input" in sys.argv:

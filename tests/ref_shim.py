@@ -335,3 +335,19 @@ def reference_problem(pkg, plate, material, accelerometer, height):
         return (mats,) + tuple(t[1:])
     P.load_matrices_unsymm = fake_load
     return P.Problem(FakeGeometry(height, plate), material, accelerometer)
+
+
+def reference_symm_problem(pkg, ff_dense, material, height):
+    """The reference's mid-plane symmetric branch (`Problem.py:228-308, 391-417`) executed as
+    written, on the dense dict of `synthetic.make_bending_plate(..., dense=True)` in place of
+    `load_matrices_symm`'s.  The branch needs `self.accelerometer is None`, which the reference's
+    own constructor refuses (`Problem.py:91-94` and `:201-204` raise when an accelerometer is
+    missing) -- it is dead code there.  To run it unmodified, a subclass pins the attribute
+    `accelerometer` to None and the constructor gets a placeholder object."""
+    P = pkg.Problem
+    P.load_matrices_symm = lambda geom_file: geom_file
+
+    class SymmetricBranch(P.Problem):
+        accelerometer = property(lambda self: None, lambda self, value: None)
+
+    return SymmetricBranch(FakeGeometry(height, ff_dense), material, object())
