@@ -200,7 +200,16 @@ struct jpb_state {
     bool timing = true;
     int nstreams = 1;                  // sub-waves of a fused evaluation run concurrently
     std::vector<cudaStream_t> aux;
+    std::vector<cudaStream_t> lvl;     // side streams of LevelFork (independent launches of one tree level)
 
+    void ensure_level_streams(int n) {
+        while ((int)lvl.size() < n) {
+            cudaStream_t q;
+            if (cudaStreamCreateWithFlags(&q, cudaStreamNonBlocking) != cudaSuccess)
+                throw std::runtime_error("cudaStreamCreate failed");
+            lvl.push_back(q);
+        }
+    }
     void ensure_streams(int n) {
         while ((int)aux.size() < n) {
             cudaStream_t q;
@@ -211,6 +220,7 @@ struct jpb_state {
     }
     ~jpb_state() {
         for (auto q : aux) cudaStreamDestroy(q);
+        for (auto q : lvl) cudaStreamDestroy(q);
         for (auto e : pool) cudaEventDestroy(e);
         if (stream) cudaStreamDestroy(stream);
         if (counters) cudaFree(counters);
@@ -324,6 +334,12 @@ struct Tuning {
     // (measured at cfg1, factor phase: off 50.6 ms, 48 KB 50.3, 72 KB 52.1, 110 KB 54.0; DRAM traffic of
     // the classes it replaces 45 -> 40 GB: these fronts are bound by their pivot chain, not by memory)
     int panel_max = 48, panel_nt64 = 48, panel_nt128 = 96;
+    // launches of one elimination-tree level (one per size class / kernel kind) are independent: run
+    // them on side streams so that the narrow ones fill the SMs the wide ones leave idle.  Default off:
+    // measured (profiles/r2_summary.md section 11) the factor phase gains 2 % at cfg1 (50.3 -> 49.3 ms), 1 % at
+    // cfg4, the solves nothing, and the ~400 extra event calls per evaluation make the device-resident
+    // arm host-bound (78.7 -> 90.8 ms per step)
+    int fork = 0;
     Tuning() {
         auto geti = [](const char* name, int def) {
             const char* v = getenv(name);
@@ -346,6 +362,7 @@ struct Tuning {
         panel_max = std::min(200, geti("JPB_PANEL_MAX", panel_max));
         panel_nt64 = geti("JPB_PANEL_NT64", panel_nt64);
         panel_nt128 = geti("JPB_PANEL_NT128", panel_nt128);
+        fork = geti("JPB_FORK", fork);
     }
 };
 // symbolic options, overridable for tuning runs (JPB_LEAF, JPB_RELAX_SMALL, ...)
@@ -392,14 +409,54 @@ const double* assemble_entries(jpb_state* st, cudaStream_t s, Pattern& P, int ns
     return nullptr;
 }
 
+// The launches of one level of the elimination tree touch disjoint fronts: the first goes to the
+// caller's stream, the others to side streams that wait for the level to open (everything the
+// caller's stream held before) and are joined before the next level.  Same kernels, same
+// results; only the tails of the narrow launches overlap with the wide ones.
+struct LevelFork {
+    static constexpr int NSIDE = 3;
+    jpb_state* st;
+    cudaStream_t s;
+    bool on;
+    int k = 0;
+    bool touched[NSIDE] = {false, false, false};
+    LevelFork(jpb_state* st_, cudaStream_t s_, int nlaunches) : st(st_), s(s_), on(tuning().fork && nlaunches > 1) {
+        if (on) {
+            st->ensure_level_streams(NSIDE);
+            cudaEvent_t open = st->ev();
+            CK(cudaEventRecord(open, s));
+            for (int i = 0; i < NSIDE && i < nlaunches - 1; ++i) {
+                CK(cudaStreamWaitEvent(st->lvl[i], open, 0));
+                touched[i] = true;
+            }
+        }
+    }
+    cudaStream_t next() {
+        const int i = k++;
+        if (!on || i == 0) return s;
+        return st->lvl[(i - 1) % NSIDE];
+    }
+    void join() {
+        if (!on) return;
+        for (int i = 0; i < NSIDE; ++i)
+            if (touched[i]) {
+                cudaEvent_t done = st->ev();
+                CK(cudaEventRecord(done, st->lvl[i]));
+                CK(cudaStreamWaitEvent(s, done, 0));
+            }
+    }
+};
+
 // numeric factorisation of `nsys` systems into F.  ent_order: `data` is [nsys, nnz] in
 // front-entry order (from assemble_entries) instead of the caller's CSC order.
-void factor(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* F, const cd* data, bool ent_order,
+void factor(jpb_state* st, cudaStream_t s0, Pattern& P, int nsys, cd* F, const cd* data, bool ent_order,
             int* status) {
-    Span span(st, s, PH_FACTOR);
+    Span span(st, s0, PH_FACTOR);
     for (int l = 0; l < P.S.nlevels; ++l) {
         const int* lfl = P.d_flf + P.flevelptr[l];
+        LevelFork lf_fork(st, s0, (int)P.fgroups[l].size());
         for (const Pattern::FactorGroup& g : P.fgroups[l]) {
+            cudaStream_t s = lf_fork.next();
             const int64_t grid64 = (int64_t)g.count * nsys;
             if (grid64 > 0x7fffffff) throw InvalidArg("wave too large for one launch");
             const unsigned grid = (unsigned)grid64;
@@ -427,6 +484,7 @@ void factor(jpb_state* st, cudaStream_t s, Pattern& P, int nsys, cd* F, const cd
 #undef JPB_FACTOR
             launch_check(st);
         }
+        lf_fork.join();
     }
 }
 
@@ -455,8 +513,8 @@ void scale_vectors(jpb_state* st, cudaStream_t s, Pattern& P, const double* scal
 
 // x(b, j) = A_b^-1 rhs(b, j)  (or A_b^-T)
 constexpr int WSOLVE_NW = 8;     // systems (warps) per CTA of the warp-per-system solve kernels
-void tri_solve(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool trans, VecView vv, int phase) {
-    Span span(st, s, phase);
+void tri_solve(jpb_state* st, cudaStream_t s0, Pattern& P, const cd* F, bool trans, VecView vv, int phase) {
+    Span span(st, s0, phase);
     const size_t smem = (size_t)P.max_s * sizeof(cd);
     const int64_t mult = (int64_t)vv.nsys * vv.nrhs;
     const int64_t wgroups = (mult + WSOLVE_NW - 1) / WSOLVE_NW;
@@ -468,9 +526,11 @@ void tri_solve(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool tran
         const int* lf = P.d_levelfronts + P.levelptr[l];
         const int nbig = std::min(P.cls[l][0], nabove), nmid = std::min(P.cls[l][1], nabove - nbig);
         const int cnt[3] = {nbig, nmid, nabove - nbig - nmid};
+        LevelFork lf_fork(st, s0, (cnt[0] > 0) + (cnt[1] > 0) + (cnt[2] > 0) + (n > nabove));
         int off = 0;
         for (int c = 0; c < 3; ++c) {
             if (!cnt[c]) continue;
+            cudaStream_t s = lf_fork.next();
             const int64_t grid64 = (int64_t)cnt[c] * mult;
             if (grid64 > 0x7fffffff) throw InvalidArg("wave too large for one launch");
             const unsigned grid = (unsigned)grid64;
@@ -499,6 +559,7 @@ void tri_solve(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool tran
             const int vstride = (P.wsolve[l][1] + 1) & ~1;
             const size_t wsmem = (size_t)WSOLVE_NW * (vstride + TW) * sizeof(cd);
             const int* lfw = lf + nabove;
+            cudaStream_t s = lf_fork.next();
             if (fwd) {
                 if (trans) fwd_warp_kernel<true, WSOLVE_NW><<<grid, WSOLVE_NW * 32, wsmem, s>>>(P.sd, lfw, F, vv, vstride);
                 else fwd_warp_kernel<false, WSOLVE_NW><<<grid, WSOLVE_NW * 32, wsmem, s>>>(P.sd, lfw, F, vv, vstride);
@@ -508,6 +569,7 @@ void tri_solve(jpb_state* st, cudaStream_t s, Pattern& P, const cd* F, bool tran
             }
             launch_check(st);
         }
+        lf_fork.join();
     };
     for (int l = 0; l < P.S.nlevels; ++l) level(l, true);
     for (int l = P.S.nlevels - 1; l >= 0; --l) level(l, false);
