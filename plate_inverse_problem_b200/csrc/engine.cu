@@ -340,6 +340,10 @@ struct Tuning {
     // cfg4, the solves nothing, and the ~400 extra event calls per evaluation make the device-resident
     // arm host-bound (78.7 -> 90.8 ms per step)
     int fork = 0;
+    // a launch of the 256-thread class with no more CTAs than SMs (the one- and two-front levels at the
+    // top of the elimination tree of a wave that memory limits to ~one system per SM) runs with 512
+    // threads per front instead: one CTA per SM either way, twice the warps to hide its latencies
+    int wide = 1;
     Tuning() {
         auto geti = [](const char* name, int def) {
             const char* v = getenv(name);
@@ -363,6 +367,7 @@ struct Tuning {
         panel_nt64 = geti("JPB_PANEL_NT64", panel_nt64);
         panel_nt128 = geti("JPB_PANEL_NT128", panel_nt128);
         fork = geti("JPB_FORK", fork);
+        wide = geti("JPB_WIDE", wide);
     }
 };
 // symbolic options, overridable for tuning runs (JPB_LEAF, JPB_RELAX_SMALL, ...)
@@ -477,6 +482,7 @@ void factor(jpb_state* st, cudaStream_t s0, Pattern& P, int nsys, cd* F, const c
                     if (ent_order) factor_level_kernel<true, 256, true><<<grid, 256, GB_SMEM, s>>>(P.sd, lf, nsys, F, data, status);
                     else factor_level_kernel<false, 256, true><<<grid, 256, GB_SMEM, s>>>(P.sd, lf, nsys, F, data, status);
                 }
+                else if (g.nt == 256 && tuning().wide && grid <= (unsigned)st->sm_count) { JPB_FACTOR(factor_level_kernel, 512) }
                 else if (g.nt == 256) { JPB_FACTOR(factor_level_kernel, 256) }
                 else if (g.nt == 128) { JPB_FACTOR(factor_level_kernel, 128) }
                 else { JPB_FACTOR(factor_level_kernel, 64) }

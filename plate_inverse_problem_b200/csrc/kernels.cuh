@@ -773,7 +773,7 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
     constexpr int NW = NT / 32;
     // warp tile: 16 rows x WC columns.  JPB_WN = 0: 16 x 32 for the 256-thread class (operand reuse
     // on the large fronts), 16 x 16 for the narrower ones (no register spills, more tiles per warp)
-    constexpr int WN = JPB_WN ? JPB_WN : (NT == 256 ? 4 : 2), WC = 8 * WN;
+    constexpr int WN = JPB_WN ? JPB_WN : (NT >= 256 ? 4 : 2), WC = 8 * WN;
     constexpr int FACTOR_THREADS = NT;
     const int b = blockIdx.x % nsys;
     const FrontDesc fd = sd.fr[level_fronts[blockIdx.x / nsys]];
