@@ -119,6 +119,7 @@ struct Pattern {
         int smem;           // dynamic shared bytes (0 for the global-memory kernel)
         int nt;
         int kind;           // 0: factor_level_kernel, 1: factor_smem_kernel, 2: factor_panel_kernel
+        int maxm;           // largest contribution-block order in the group (bands of schur_band_kernel)
     };
     std::vector<int> flevelptr;
     int* d_flf = nullptr;
@@ -344,6 +345,12 @@ struct Tuning {
     // top of the elimination tree of a wave that memory limits to ~one system per SM) runs with 512
     // threads per front instead: one CTA per SM either way, twice the warps to hide its latencies
     int wide = 1;
+    // 256-thread class: groups whose largest contribution block has at least this order compute their
+    // contribution blocks in schur_band_kernel (several CTAs per front) instead of inside the factor
+    // kernel.  0 = never, the default: measured at cfg4 (profiles/r2_summary.md section 13) the split
+    // halves the DRAM traffic of the large-front levels (level 12: 65 -> 33 GB) and leaves their time
+    // where it was (18.6 -> 19.9 ms): the contribution-block GEMM already runs at ~75 % of the DMMA peak
+    int schur_split = 0;
     Tuning() {
         auto geti = [](const char* name, int def) {
             const char* v = getenv(name);
@@ -368,6 +375,7 @@ struct Tuning {
         panel_nt128 = geti("JPB_PANEL_NT128", panel_nt128);
         fork = geti("JPB_FORK", fork);
         wide = geti("JPB_WIDE", wide);
+        schur_split = geti("JPB_SCHUR_SPLIT", schur_split);
     }
 };
 // symbolic options, overridable for tuning runs (JPB_LEAF, JPB_RELAX_SMALL, ...)
@@ -481,6 +489,22 @@ void factor(jpb_state* st, cudaStream_t s0, Pattern& P, int nsys, cd* F, const c
                 if (g.nt == 256 && tuning().tma) {
                     if (ent_order) factor_level_kernel<true, 256, true><<<grid, 256, GB_SMEM, s>>>(P.sd, lf, nsys, F, data, status);
                     else factor_level_kernel<false, 256, true><<<grid, 256, GB_SMEM, s>>>(P.sd, lf, nsys, F, data, status);
+                }
+                else if (g.nt == 256 && tuning().schur_split > 0 && g.maxm >= tuning().schur_split) {
+                    // pivot panels here, contribution blocks in a launch of their own (several CTAs per front)
+                    const bool wide = tuning().wide && grid <= (unsigned)st->sm_count;
+                    if (wide) {
+                        if (ent_order) factor_level_kernel<true, 512, false, false><<<grid, 512, 0, s>>>(P.sd, lf, nsys, F, data, status);
+                        else factor_level_kernel<false, 512, false, false><<<grid, 512, 0, s>>>(P.sd, lf, nsys, F, data, status);
+                    } else {
+                        if (ent_order) factor_level_kernel<true, 256, false, false><<<grid, 256, 0, s>>>(P.sd, lf, nsys, F, data, status);
+                        else factor_level_kernel<false, 256, false, false><<<grid, 256, 0, s>>>(P.sd, lf, nsys, F, data, status);
+                    }
+                    launch_check(st);
+                    const int nbands = (g.maxm + SCHUR_BAND - 1) / SCHUR_BAND;
+                    const int64_t g2 = grid64 * nbands;
+                    if (g2 > 0x7fffffff) throw InvalidArg("wave too large for one launch");
+                    schur_band_kernel<256><<<(unsigned)g2, 256, 0, s>>>(P.sd, lf, nsys, F, nbands);
                 }
                 else if (g.nt == 256 && tuning().wide && grid <= (unsigned)st->sm_count) { JPB_FACTOR(factor_level_kernel, 512) }
                 else if (g.nt == 256) { JPB_FACTOR(factor_level_kernel, 256) }
@@ -1109,8 +1133,9 @@ int jpb_add_mat(jpb_state* st, int64_t N, int64_t nnz, const void* indices, cons
                 auto& groups = P->fgroups[l];
                 if (groups.empty() || groups.back().kind != it.kind || groups.back().nt != it.nt ||
                     groups.back().smem != it.smem)
-                    groups.push_back({(int)q, 0, it.smem, it.nt, it.kind});
+                    groups.push_back({(int)q, 0, it.smem, it.nt, it.kind, 0});
                 groups.back().count++;
+                groups.back().maxm = std::max(groups.back().maxm, S.f_s[it.f] - S.f_k[it.f]);
                 flf.push_back(it.f);
             }
         }

@@ -751,7 +751,7 @@ constexpr int KMAX = 32;   // component matrices supported by the fused assembly
 //   TMA = true (NT = 256 only): the strip updates of every 64-column super tile and the Schur
 //                  complement run through cta_gemm (operand panels staged in dynamic shared
 //                  memory by bulk asynchronous copies); launch with GB_SMEM dynamic bytes
-template <bool ENT_ORDER, int NT, bool TMA = false>
+template <bool ENT_ORDER, int NT, bool TMA = false, bool SCHUR = true>
 __global__ void __launch_bounds__(NT, JPB_OCC / NT)
 factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd* Fall,
                     const cd* __restrict__ data, int* status) {
@@ -949,6 +949,8 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
         __syncthreads();
     }
     // ---- contribution block: C = sum over children of their blocks (gathered) - Lt * U
+    // (SCHUR = false: left to schur_band_kernel, which spreads it over several CTAs per front)
+    if constexpr (SCHUR) {
     const int m = s - k;
     if (TMA && m > 0) {
         cd* C = F + (int64_t)k * ld + k;
@@ -969,7 +971,51 @@ factor_level_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, c
             store_tile_cb<2, WN>(acc, F + (int64_t)r * ld + c, ld, mr, nc, rc, cc, sd, fd, chs, Fsys, lane);
         }
     }
+    }
     if (tid == 0 && ts.sing && status) atomicOr(status + b, 1);
+}
+
+// Contribution blocks of large fronts as a launch of their own: C = gathered children - Lt * U on
+// `nbands` CTAs per (front, system), each taking a band of SCHUR_BAND columns.  Why: with one CTA per
+// front, 296 fronts of ~10 MB are in flight and the m x k panel of Lt that every 32-column block of C
+// re-reads comes from DRAM each time (cfg4: 3-4x the compulsory traffic, the launches run at 3.6 TB/s).
+// The CTAs of one front sit next to each other in the grid, run at the same time and walk Lt in the
+// same order, so the panel is fetched from DRAM once and served to the other bands by L2.
+constexpr int SCHUR_BAND = 128;
+template <int NT>
+__global__ void __launch_bounds__(NT, JPB_OCC / NT)
+schur_band_kernel(SymDev sd, const int* __restrict__ level_fronts, int nsys, cd* Fall, int nbands) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = NT / 32, WN = 4, WC = 8 * WN;
+    int bid = blockIdx.x;
+    const int band = bid % nbands;
+    bid /= nbands;
+    const int b = bid % nsys;
+    const FrontDesc fd = sd.fr[level_fronts[bid / nsys]];
+    const int s = fd.s, k = fd.k, ld = fd.ld, m = s - k;
+    const int c0 = band * SCHUR_BAND;
+    if (c0 >= m) return;
+    cd* Fsys = Fall + (int64_t)b * sd.front_slots;
+    cd* F = Fsys + fd.off;
+    __shared__ ChildInfo chs[MAXCH];
+    if (tid < fd.nchild && tid < MAXCH) {
+        const FrontDesc fc = sd.fr[sd.children[fd.childptr + tid]];
+        chs[tid].cb = fc.off + (int64_t)fc.k * fc.ld + fc.k;
+        chs[tid].ld = fc.ld;
+        chs[tid].invoff = fc.invoff;
+    }
+    __syncthreads();
+    const int bw = min(SCHUR_BAND, m - c0);
+    const int ntr = (m + 15) >> 4, ntc = (bw + WC - 1) / WC;
+    for (int tile = warp; tile < ntr * ntc; tile += NW) {
+        const int rc = 16 * (tile % ntr), cc = c0 + WC * (tile / ntr);      // within the block
+        const int r = k + rc, c = k + cc;
+        const int mr = min(16, s - r), nc = min(WC, s - c);
+        Acc<2, WN> acc;
+        acc.zero();
+        warp_gemm<2, WN>(acc, F + (int64_t)r * ld, ld, mr, F + c, ld, nc, k, lane);
+        store_tile_cb<2, WN>(acc, F + (int64_t)r * ld + c, ld, mr, nc, rc, cc, sd, fd, chs, Fsys, lane);
+    }
 }
 
 // ------------------------------------------------- shared-memory-resident fronts (K2s)
