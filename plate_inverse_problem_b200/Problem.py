@@ -183,8 +183,12 @@ class Problem:
     # ---- forward -------------------------------------------------------------------------
     def _forward_raw(self, freqs, params, return_u=False):
         freqs = np.atleast_1d(np.asarray(freqs, dtype=np.float64))
-        coef, s, _, _ = self.coefficients(freqs, params)
         F = freqs.size
+        if F == 0:      # an empty sweep (the reference's vmap over zero frequencies returns an empty array)
+            R = self.Q.shape[0]
+            empty_u = np.zeros((0, self.mat_size), dtype=np.complex128)
+            return (np.zeros(0), np.zeros((0, R), dtype=np.complex128)) + ((empty_u,) if return_u else ())
+        coef, s, _, _ = self.coefficients(freqs, params)
         coef, s = np.ascontiguousarray(coef), np.ascontiguousarray(s)
         y = np.zeros((F, self.Q.shape[0]), dtype=np.complex128)
         u = np.zeros((F, self.mat_size), dtype=np.complex128) if return_u else None

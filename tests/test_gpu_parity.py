@@ -788,3 +788,48 @@ def test_shaped_plate_fused_path_against_oracle():
     assert abs(L - L_x) <= max(TOL_LG * abs(L_x), 4 * abs(L_o - L_x))
     assert relerr(g, g_x) <= max(TOL_LG, 4 * relerr(g_o, g_x))
     assert abs(L - L_o) <= 1e-7 * abs(L_o) and relerr(g, g_o) <= 1e-7
+
+
+def test_edge_sizes_and_argument_errors(state, tiny):
+    """Empty and one-element sweeps, ragged shard sizes, and the error behaviour of the boundary
+    (`InnerState.h:187-232`: runtime_error "Invalid `mode`"; here every bad argument is a RuntimeError
+    with the library's message, never a crash)."""
+    from plate_inverse_problem_b200 import _lib
+    prob = tiny.problem()
+    assert prob.solveForward(np.zeros(0)).shape == (0,)
+    freqs = np.array([55.0, 140.0, 333.0])
+    fr = prob.solveForward(freqs)
+    for i, f in enumerate(freqs):                       # one frequency at a time = the sweep
+        assert abs(prob.solveForward([f])[0] - fr[i]) <= 1e-13 * fr[i]
+    ref = fr * 1.1
+    L1, g1 = prob.getLossFunction(freqs[:1], ref[:1], "MSE").value_and_grad(PARAMS)
+    L1_o, g1_o, _ = tiny.op.loss_and_grad(freqs[:1], PARAMS, ref[:1], "MSE")
+    assert abs(L1 - L1_o) <= TOL_LG * abs(L1_o) and relerr(g1, g1_o) <= TOL_LG
+    with pytest.raises(ValueError, match="not supported"):
+        prob.getLossFunction(freqs, ref, "L1")
+    with pytest.raises(ValueError, match="imaginary"):
+        prob.getLossFunction(freqs, ref * (1 + 1j), "MSE")
+    # the C-ABI itself
+    num = _register(state, tiny)
+    st, n = state._st, tiny.native
+    data, _, _ = tiny.data(freqs)
+    b = np.ones((3, tiny.N), dtype=np.complex128)
+    out = np.zeros_like(b)
+    args = (_lib.ptr(np.ascontiguousarray(data)), _lib.ptr(b))
+    assert st.lib.jpb_solve(st.h, num, 7, 0, *args, 3, 0, _lib.ptr(out), None) == _lib.JPB_EINVAL
+    assert b"Invalid `mode`" in st.lib.jpb_last_error(st.h)
+    assert st.lib.jpb_solve(st.h, num + 100, 3, 0, *args, 3, 0, _lib.ptr(out), None) == _lib.JPB_EINVAL
+    assert st.lib.jpb_solve(st.h, num, 3, 0, *args, 0, 0, _lib.ptr(out), None) == _lib.JPB_EINVAL        # empty batch
+    assert st.lib.jpb_solve(st.h, num, 3, 0, None, _lib.ptr(b), 3, 0, _lib.ptr(out), None) == _lib.JPB_EINVAL
+    assert st.lib.jpb_matvec(st.h, num, 3, 0, *args, -1, 0, _lib.ptr(out)) == _lib.JPB_EINVAL
+    with pytest.raises(RuntimeError, match="Invalid `mode`"):
+        state.solve(data, b, num, False, 0, 9)
+    with pytest.raises(RuntimeError, match="do not fit"):
+        state.solve(data[:, :-1], b, num, False, 0, 3)
+    with pytest.raises(RuntimeError, match="batch sizes"):
+        state.solve(data, b[:2], num, False, 0, 3)
+    # the state is still usable after the refused calls
+    x = state.solve(data, b, num, False, 0, 3)
+    for i in range(3):
+        A = _csc(tiny, data[i])
+        assert np.max(np.abs(A @ x[i] - b[i])) <= 1e-10 * np.max(abs(A) @ np.abs(x[i]) + 1.0)
