@@ -1613,6 +1613,13 @@ fwd_level_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __re
     for (int i = tid; i < s; i += SOLVE_THREADS) Vf[i] = v[i];
 }
 
+#ifndef JPB_BWD_UNROLL
+#define JPB_BWD_UNROLL 8
+#endif
+// rows in flight per lane in the transposed backward sweep (lane per column, warps stride the rows).  Measured:
+// 8 instead of 4 takes the adjoint solves from 32.9 to 30.1 ms at cfg4 and from 11.3 to 10.8 ms at cfg1; the same
+// change in the plain sweep (warp per row) costs 5 %, so that loop stays at 4.
+constexpr int BWD_UNROLL = JPB_BWD_UNROLL;
 // Backward sweep over one level.  TRANS = false: Ubar ; TRANS = true: Lt^T.
 template <bool TRANS, int NT>
 __global__ void __launch_bounds__(NT)
@@ -1664,7 +1671,7 @@ bwd_level_kernel(SymDev sd, const int* __restrict__ level_fronts, const cd* __re
             // v[j0+q] -= sum_{i >= j1} Lt[i, j0+q] v[i] : lane per column, warps stride the rows
             cd acc = make_double2(0.0, 0.0);
             if (lane < jw) {
-#pragma unroll 4
+#pragma unroll BWD_UNROLL
                 for (int i = j1 + warp; i < s; i += NW) cfma(acc, F[(int64_t)i * ld + j0 + lane], v[i]);
             }
             part[warp][lane] = acc;
