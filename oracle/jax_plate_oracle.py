@@ -5,16 +5,21 @@ This file is a numpy/scipy restatement of the reference algorithm.  It is import
 checker / the timed CPU baseline — never by the product package
 `plate_inverse_problem_b200` (which fails loudly when its CUDA library is missing).
 
-PARITY UNPINNED: the arithmetic of the reference lives in UMFPACK (SuiteSparse v5.x,
-`/root/reference/README.md:27`; not vendored, no pin file) which is absent from this image,
-as are jax and FreeFem++; the reference's own golden numbers
-(`examples/cpu_benchmark.py:24,35`, `examples/basics.py:30-33`) need a FreeFem++ mesh and
-cannot be regenerated here.  The linear solves below therefore use scipy's SuperLU
-(`scipy.sparse.linalg.splu`, complex128) as a stand-in for `umfpack_zi_numeric/solve`
-with the same call structure (one numeric factorisation + one solve per batch item,
-`UMFPACK_A` / `UMFPACK_Aat` = plain transpose), cross-checked by residuals and, at small
-N, by dense `numpy.linalg.solve`.  The integer index construction *is* pinned: it is
-bit-compared against scipy's own coo->csc machinery that the reference calls.
+PARITY STATUS: pinned to the reference's own code except for the arithmetic inside UMFPACK.
+`tests/ref_shim.py` executes `/root/reference/source/jax_plate/*.py` unmodified (numpy `jax`
+shim) on top of the reference's pybind11 module compiled from its sources (`oracle/Makefile`),
+and `tests/golden/make_reference_golden.py` stores what that run produces
+(`tests/golden/ref_*.npz`: index arrays, material transforms, FRF, losses, batching modes,
+AD rules, `Compressor`, optimiser trajectories, the mid-plane symmetric branch);
+`tests/test_reference_pin.py` and `tests/test_symm.py` hold the functions below to those
+values.  What stays unpinned ("parity unpinned" at the level of rounding): UMFPACK itself
+(SuiteSparse v5.x, `/root/reference/README.md:27`; not vendored, no pin file) is absent from
+this image, as are jax and FreeFem++, so the reference's golden numbers that need a FreeFem++
+mesh (`examples/cpu_benchmark.py:24,35`, `examples/basics.py:30-33`) cannot be regenerated.
+The linear solves use scipy's SuperLU (`splu`, complex128) as a stand-in for
+`umfpack_zi_numeric/solve` with the same call structure (one numeric factorisation + one
+solve per batch item, `UMFPACK_A` / `UMFPACK_Aat` = plain transpose), cross-checked by
+residuals, by an 80-bit refined solution and, at small N, by dense `numpy.linalg.solve`.
 
 Each function cites the reference lines it restates (paths relative to /root/reference).
 """
