@@ -2,13 +2,9 @@
 an accelerometer -> ProblemSymm.SymmetricProblem -> the fused CUDA path on the bordered system,
 against values produced by the reference's own branch (tests/golden/ref_symm.npz) and against the
 oracle restatement (tolerances of BASELINE.json: 1e-10 on the FRF, 1e-8 on loss / gradient)."""
-import os
-
 import numpy as np
 import pytest
 
-from conftest import ROOT
-from oracle import jax_plate_oracle as orc
 from test_symm import CASES, H, REF, oracle_case
 
 pytestmark = pytest.mark.gpu
