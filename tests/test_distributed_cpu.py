@@ -37,6 +37,26 @@ def _worker(rank, world, port, freqs, ref, queue):
     val, grad = parallel.sharded_value_and_grad(local_scaled, F, PARAMS.size)
     fr = parallel.sharded_gather(lambda lo, hi: case.op.forward(freqs[lo:hi], PARAMS), F)
     lo, hi = parallel.shard_range(F)
+    # the product's own sharded sweeps (Problem.getFRFunction, SymmetricProblem.getFRFunction: complex FRF as an
+    # all-reduce of interleaved doubles) with the native call replaced by the oracle
+    from types import SimpleNamespace
+    from plate_inverse_problem_b200.Problem import Problem
+    from plate_inverse_problem_b200.ProblemSymm import SymmetricProblem
+    calls = []
+
+    def fake_forward(fs, params, return_u=False):
+        calls.append(len(fs))
+        y = np.stack([case.op.forward(fs, params) * (1.0 + 0.5j)], axis=1)       # [n, 1] complex
+        return np.abs(y[:, 0]), y
+    for cls in (Problem, SymmetricProblem):
+        prob = object.__new__(cls)
+        prob._st = SimpleNamespace(device=0)
+        prob._forward_raw = fake_forward
+        out = prob.getFRFunction()(freqs, PARAMS)
+        want = case.op.forward(freqs, PARAMS) * (1.0 + 0.5j)
+        assert calls[-1] == hi - lo                       # this rank solved only its own block
+        assert np.allclose(out, np.abs(want) if cls is Problem else want, rtol=1e-12)
+        assert out.dtype == (np.float64 if cls is Problem else np.complex128)
     queue.put((rank, val, grad, fr, lo, hi))
     dist.barrier()
     dist.destroy_process_group()
