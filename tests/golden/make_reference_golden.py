@@ -301,6 +301,7 @@ def optimizer_fixture(pkg):
 SYMM_CASES = {      # name -> (nx, ny, material kind, constructor args after density, perturbation of the parameters)
     "iso_tiny": (6, 2, "Isotropic", (200e9, 77e9, 0.003), (1.1, 1.05, 2.0)),
     "ortho_small": (30, 4, "Orthotropic", (130e9, 9e9, 5e9, 0.3, 0.01), (1.1, 1.1, 1.2, 1.0, 1.5)),
+    "sol_sym_tiny": (8, 2, "SOL", ((0, 90, 90, 0), 130e9, 9e9, 5e9, 0.3, 0.01), (1.1, 1.1, 1.2, 1.0, 1.5)),
 }
 
 

@@ -5,7 +5,7 @@ oracle restatement (tolerances of BASELINE.json: 1e-10 on the FRF, 1e-8 on loss 
 import numpy as np
 import pytest
 
-from test_symm import CASES, H, REF, oracle_case
+from test_symm import CASES, H, REF, oracle_case, product_material
 
 pytestmark = pytest.mark.gpu
 TOL_FR, TOL_LG = 1e-10, 1e-8
@@ -13,12 +13,9 @@ LOSSES = ("MSE", "RMSE", "MSE_AFC", "MSE_LOG_AFC")
 
 
 def product(name, ff):
-    from plate_inverse_problem_b200 import Material
     from plate_inverse_problem_b200.Problem import Geometry, Problem
     from plate_inverse_problem_b200.ProblemSymm import SymmetricProblem
-    p, rho = REF[f"{name}_params"], float(REF[f"{name}_rho"])
-    mat = Material.Isotropic(rho, *p) if name.startswith("iso") else Material.Orthotropic(rho, *p)
-    prob = Problem(Geometry(H, ff), mat)            # no accelerometer + is_mps -> symmetric path (Problem.py:228)
+    prob = Problem(Geometry(H, ff), product_material(name))            # no accelerometer + is_mps -> symmetric path (Problem.py:228)
     assert isinstance(prob, SymmetricProblem) and prob.mat_size == ff["M"].shape[0] + 1
     return prob
 

@@ -13,14 +13,25 @@ from oracle import jax_plate_oracle as orc
 
 REF = np.load(os.path.join(ROOT, "tests", "golden", "ref_symm.npz"))
 H = 2e-3
-CASES = {"iso_tiny": (6, 2, "isotropic"), "ortho_small": (30, 4, "orthotropic")}
+CASES = {"iso_tiny": (6, 2, "isotropic"), "ortho_small": (30, 4, "orthotropic"), "sol_sym_tiny": (8, 2, "sol")}
+SOL_ANGLES = (0, 90, 90, 0)       # a mid-plane symmetric lay-up of the benchmark laminate
 
 
 def oracle_case(name):
     from plate_inverse_problem_b200.synthetic import make_bending_plate
     nx, ny, kind = CASES[name]
     ff = make_bending_plate(nx, ny)
-    return ff, orc.OracleSymmProblem(ff, orc.make_d_transform(kind, H), float(REF[f"{name}_rho"]), H)
+    return ff, orc.OracleSymmProblem(ff, orc.make_d_transform(kind, H, SOL_ANGLES), float(REF[f"{name}_rho"]), H)
+
+
+def product_material(name):
+    from plate_inverse_problem_b200 import Material
+    p, rho = REF[f"{name}_params"], float(REF[f"{name}_rho"])
+    if name.startswith("iso"):
+        return Material.Isotropic(rho, *p)
+    if name.startswith("ortho"):
+        return Material.Orthotropic(rho, *p)
+    return Material.SOL(rho, SOL_ANGLES, *p)
 
 
 @pytest.mark.parametrize("name", list(CASES))
@@ -58,10 +69,10 @@ def test_bordered_system_reproduces_the_reduced_one(name):
     """Host logic of ProblemSymm: sum_k coef_k M_k on N = n + 1 unknowns with rhs e_t has the
     solution (u, 1), u the solution of the reference's reduced system; Q (u, 1) = c0 + c.u."""
     from plate_inverse_problem_b200.ProblemSymm import bordered_components, d_coefficients_and_jacobian
-    from plate_inverse_problem_b200 import Material
     ff, op = oracle_case(name)
     p, rho = REF[f"{name}_params"], float(REF[f"{name}_rho"])
-    mat = Material.Isotropic(rho, *p) if name.startswith("iso") else Material.Orthotropic(rho, *p)
+    mat = product_material(name)
+    assert mat.is_mps
     mats = bordered_components(ff, rho, H / 2)
     coef, s, dc, ds = d_coefficients_and_jacobian(mat.get_D_transform(H), p, [100.0, 250.0], with_jacobian=True)
     assert coef.shape == (2, 8) and np.all(s == 1.0) and np.all(ds == 0.0)
