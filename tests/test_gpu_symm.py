@@ -88,3 +88,24 @@ def test_symmetric_path_candidates_jacobian_and_a_descent_step():
     lf = prob.getLossFunction(freqs, ref, "MSE_LOG_AFC", scaling_params=start)
     res = Optimizers.optimize_gd(lf, np.ones(3), N_steps=5, h=0.05)
     assert res.f_history[-1] < res.f_history[0]
+
+
+def test_complex_losses_need_a_single_readout_row():
+    """C-ABI loss types 5 / 6 (complex read-out) are refused on a pattern with three read-out rows."""
+    from conftest import PARAMS, get_case
+    from plate_inverse_problem_b200 import _lib
+    prob = get_case("tiny").problem()
+    freqs = np.array([100.0, 200.0])
+    coef, s, _, _ = prob.coefficients(freqs, PARAMS)
+    coef, s = np.ascontiguousarray(coef), np.ascontiguousarray(s)
+    ref = np.ones(2, dtype=np.complex128).view(np.float64)
+    fr, loss = np.zeros(2), np.zeros(1)
+    ct, cts = np.zeros((2, coef.shape[1]), dtype=np.complex128), np.zeros(2, dtype=np.complex128)
+    st = prob._st
+    for lt in (5, 6, 7, -1):
+        rc = st.lib.jpb_eval_loss_grad(st.h, prob.solver_num, 2, _lib.ptr(coef), _lib.ptr(s), _lib.ptr(ref),
+                                       _lib.ptr(prob.weights), lt, 2, _lib.ptr(fr), _lib.ptr(loss), _lib.ptr(ct),
+                                       _lib.ptr(cts), None)
+        assert rc == _lib.JPB_EINVAL
+        msg = st.lib.jpb_last_error(st.h)
+        assert (b"single read-out row" in msg) if lt in (5, 6) else (b"unknown loss type" in msg)
